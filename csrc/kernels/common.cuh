@@ -1,0 +1,31 @@
+// Host-side helpers shared by every .cu in libdtf_kernels: error reporting through the C ABI,
+// launch accounting (bench.py reports "gpu_launches" from it) and TMA tensor-map construction.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+namespace dtf {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+int num_sms();
+
+// 2-D bf16 tensor map with 128-byte swizzle.  `inner` is the contiguous dimension.
+// Returns false (and sets the error string) on failure.
+bool make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
+                       uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer);
+
+#define DTF_CUDA_OK(expr)                                                               \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      ::dtf::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                       __LINE__);                                                       \
+      return -1;                                                                        \
+    }                                                                                   \
+  } while (0)
+
+}  // namespace dtf

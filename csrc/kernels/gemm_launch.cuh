@@ -1,0 +1,104 @@
+// Host-side launch plumbing for gemm_sm100_kernel: tensor maps, tiling decisions, dispatch.
+#pragma once
+
+#include "common.cuh"
+#include "gemm_sm100.cuh"
+
+namespace dtf {
+
+struct GemmArgs {
+  const void* A; long long lda; bool a_mn;
+  const void* B; long long ldb; bool b_mn;
+  void* D; long long ldd;
+  int M, N, K;
+  int epi;
+  const float* bias;
+  const void* aux; long long ldaux;
+  int splits;
+  int bn;  // 0 = choose
+  // fused pull
+  bool gather;
+  const unsigned long long* row_src;
+  const void* dense_x;
+  int slots, dense_cols;
+  unsigned int* tile_flags;
+  unsigned int* chunk_counter;
+  // fused push
+  const unsigned long long* row_dst;
+  cudaStream_t stream;
+};
+
+template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
+int launch_gemm_t(const GemmArgs& a) {
+  using S = GemmSmem<BN>;
+  auto kern = gemm_sm100_kernel<BN, A_MN, B_MN, EPI, GATHER>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DTF_CUDA_OK(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    DTF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_set[dev & 63] = true;
+  }
+  CUtensorMap tmA, tmB;
+  if (!A_MN) {
+    if (!make_tmap_bf16_2d(&tmA, a.A, (uint64_t)a.K, (uint64_t)a.M, (uint64_t)a.lda * 2, BK, BM)) return -1;
+  } else {
+    if (!make_tmap_bf16_2d(&tmA, a.A, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda * 2, 64, BK)) return -1;
+  }
+  if (!B_MN) {
+    if (!make_tmap_bf16_2d(&tmB, a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb * 2, BK, BN)) return -1;
+  } else {
+    if (!make_tmap_bf16_2d(&tmB, a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb * 2, 64, BK)) return -1;
+  }
+  GemmParams p{};
+  p.M = a.M; p.N = a.N; p.K = a.K;
+  p.m_tiles = (a.M + BM - 1) / BM;
+  p.n_tiles = (a.N + BN - 1) / BN;
+  const int total_kb = (a.K + BK - 1) / BK;
+  int splits = a.splits < 1 ? 1 : a.splits;
+  if (splits > total_kb) splits = total_kb;
+  p.k_blocks_per_split = (total_kb + splits - 1) / splits;
+  p.splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+  p.D = a.D; p.ldd = a.ldd;
+  p.bias = a.bias;
+  p.aux = reinterpret_cast<const __nv_bfloat16*>(a.aux); p.ldaux = a.ldaux;
+  p.row_src = a.row_src;
+  p.dense_x = reinterpret_cast<const __nv_bfloat16*>(a.dense_x);
+  p.a_buf = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(a.A));
+  p.lda_buf = a.lda;
+  p.slots = a.slots; p.dense_cols = a.dense_cols;
+  p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter;
+  p.row_dst = a.row_dst;
+  const int tiles = p.m_tiles * p.n_tiles * p.splits;
+  int grid = tiles < num_sms() ? tiles : num_sms();
+  if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of idle CTAs still pull rows
+  const int threads = GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads;
+  kern<<<grid, threads, S::kTotal, a.stream>>>(tmA, tmB, p);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// picks the N tile that wastes the fewest SM-waves for this shape
+inline int choose_bn(int M, int N, int splits) {
+  const int sms = num_sms();
+  const int cand[3] = {256, 128, 64};
+  int best = 256;
+  double best_cost = 1e30;
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cand[i];
+    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn) * (splits < 1 ? 1 : splits);
+    const long long waves = (tiles + sms - 1) / sms;
+    // per-tile cost ~ bn (MMA time) plus a fixed overhead that penalises tiny tiles
+    const double cost = (double)waves * (bn + 24.0);
+    if (cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
+}
+
+int launch_gemm_kk(const GemmArgs& a);    // A K-major,  B K-major   (forward)
+int launch_gemm_kmn(const GemmArgs& a);   // A K-major,  B MN-major  (dgrad)
+int launch_gemm_mnmn(const GemmArgs& a);  // A MN-major, B MN-major  (wgrad)
+int launch_gemm_gather(const GemmArgs& a);  // fused pull: gather warps + forward GEMM
+
+}  // namespace dtf

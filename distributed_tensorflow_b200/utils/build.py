@@ -1,0 +1,117 @@
+"""In-tree native builds.
+
+Two shared libraries are produced under ``distributed_tensorflow_b200/_lib``:
+
+* ``libdtf_kernels.so`` -- every ``csrc/kernels/*.cu`` compiled by nvcc for sm_100a only
+  (``-gencode arch=compute_100a,code=sm_100a -lineinfo``); the CUDA runtime is linked statically so
+  the library loads on a GPU-less box (nvcc cross-compiles there).
+* ``libdtf_native.so`` -- the CPU runtime in ``csrc/native/*.cc`` (checkpoint-V2 bundle writer /
+  reader, crc32c, SSTable, TCP parameter-server transport, named queues, optimizer apply).
+
+Objects are cached by source mtime so that a rebuild only recompiles what changed.  The ``.so``
+files stay in the tree (git-ignored) so that they travel with the repository snapshot.
+"""
+from __future__ import annotations
+
+import concurrent.futures as cf
+import os
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parents[2]
+CSRC = REPO / "csrc"
+LIB_DIR = REPO / "distributed_tensorflow_b200" / "_lib"
+OBJ_DIR = REPO / "build" / "obj"
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC",
+    "-Xcompiler", "-Wno-unused-function",
+]
+CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread", "-msse4.2"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and Path(cand).exists():
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def _newest_header_mtime(d: Path) -> float:
+    m = 0.0
+    for pat in ("*.cuh", "*.h", "*.hpp"):
+        for p in d.glob(pat):
+            m = max(m, p.stat().st_mtime)
+    for p in (REPO / "include").glob("*.h"):
+        m = max(m, p.stat().st_mtime)
+    return m
+
+
+def _run(cmd: list[str]) -> None:
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("command failed: %s\n%s\n%s" % (" ".join(cmd), r.stdout, r.stderr))
+
+
+def _compile_all(srcs: list[Path], mk_cmd, tag: str, jobs: int) -> list[Path]:
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    objs, todo = [], []
+    for s in srcs:
+        o = OBJ_DIR / (tag + "_" + s.stem + ".o")
+        objs.append(o)
+        dep_m = max(s.stat().st_mtime, _newest_header_mtime(s.parent))
+        if not o.exists() or o.stat().st_mtime < dep_m:
+            todo.append((s, o))
+    if todo:
+        with cf.ThreadPoolExecutor(max_workers=jobs) as ex:
+            futs = [ex.submit(_run, mk_cmd(s, o)) for s, o in todo]
+            for f in futs:
+                f.result()
+    return objs
+
+
+def build_kernels(force: bool = False, jobs: int | None = None, verbose: bool = False) -> Path:
+    """Compile csrc/kernels/*.cu -> _lib/libdtf_kernels.so (sm_100a)."""
+    srcs = sorted((CSRC / "kernels").glob("*.cu"))
+    out = LIB_DIR / "libdtf_kernels.so"
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    if force and OBJ_DIR.exists():
+        for o in OBJ_DIR.glob("k_*.o"):
+            o.unlink()
+    nvcc = _nvcc()
+    extra = ["-Xptxas", "-v"] if verbose else []
+    objs = _compile_all(
+        srcs, lambda s, o: [nvcc, *NVCC_FLAGS, *extra, "-I", str(REPO / "include"), "-c", str(s), "-o", str(o)],
+        "k", jobs or min(8, os.cpu_count() or 4))
+    if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
+        _run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static",
+              "-Xcompiler", "-fPIC", "-o", str(out), *map(str, objs), "-lpthread", "-ldl", "-lrt"])
+    return out
+
+
+def build_native(force: bool = False, jobs: int | None = None) -> Path:
+    """Compile csrc/native/*.cc -> _lib/libdtf_native.so (CPU runtime)."""
+    srcs = sorted((CSRC / "native").glob("*.cc"))
+    out = LIB_DIR / "libdtf_native.so"
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    if force and OBJ_DIR.exists():
+        for o in OBJ_DIR.glob("n_*.o"):
+            o.unlink()
+    cxx = os.environ.get("CXX", "g++")
+    objs = _compile_all(
+        srcs, lambda s, o: [cxx, *CXX_FLAGS, "-I", str(REPO / "include"), "-c", str(s), "-o", str(o)],
+        "n", jobs or min(8, os.cpu_count() or 4))
+    if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
+        _run([cxx, "-shared", "-pthread", "-o", str(out), *map(str, objs)])
+    return out
+
+
+def build_all(force: bool = False, verbose: bool = False) -> dict:
+    return {"kernels": str(build_kernels(force=force, verbose=verbose)), "native": str(build_native(force=force))}
+
+
+if __name__ == "__main__":
+    print(build_all(force="--force" in sys.argv, verbose="-v" in sys.argv))
