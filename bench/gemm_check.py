@@ -44,9 +44,12 @@ def main():
         b = torch.randn(N, device=dev)
         ref = torch.relu(x.float() @ w.float().t() + b)
         for bn in (0, 64, 128, 256):
-            y = G.linear_fw(x, w, b, relu=True, bn=bn)
+            mo = torch.zeros(M, G.mask_words(N), dtype=torch.int32, device=dev)
+            y = G.linear_fw(x, w, b, relu=True, bn=bn, mask_out=mo)
             torch.cuda.synchronize()
             e = rel_err(y, ref)
+            if not torch.equal(G.unpack_mask(mo, N), y > 0):
+                e = 1.0  # mask mismatch
             row = {"op": "fw", "M": M, "N": N, "K": K, "bn": bn, "rel_err": e}
             if bn == 0 or M >= 8192:
                 t = timeit(lambda: G.linear_fw(x, w, b, relu=True, bn=bn))
@@ -60,7 +63,8 @@ def main():
         dy = (torch.randn(M, N, device=dev) * 0.5).bfloat16()
         w = (torch.randn(N, K, device=dev) * 0.05).bfloat16()
         h = torch.relu(torch.randn(M, K, device=dev)).bfloat16()
-        ref = (dy.float() @ w.float()) * (h.float() > 0)
+        h = G.pack_mask(h > 0)
+        ref = (dy.float() @ w.float()) * G.unpack_mask(h, K)
         for bn in (0, 128, 256):
             dx = G.linear_dx(dy, w, h, bn=bn)
             torch.cuda.synchronize()

@@ -13,7 +13,7 @@ struct GemmArgs {
   int M, N, K;
   int epi;
   const float* bias;
-  const void* aux; long long ldaux;
+  const uint32_t* mask_in; uint32_t* mask_out; long long ldmask;
   int splits;
   int bn;  // 0 = choose
   // fused pull
@@ -50,6 +50,15 @@ int launch_gemm_t(const GemmArgs& a) {
   } else {
     if (!make_tmap_bf16_2d(&tmB, a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb * 2, 64, BK)) return -1;
   }
+  CUtensorMap tmD;
+  constexpr bool kOutF32 = (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC);
+  if (EPI != EPI_PUSH_ROWS) {
+    if (!make_tmap_2d(&tmD, a.D, kOutF32 ? 4 : 2, (uint64_t)a.N, (uint64_t)a.M,
+                      (uint64_t)a.ldd * (kOutF32 ? 4 : 2), kOutF32 ? 32 : 64, 32))
+      return -1;
+  } else {
+    tmD = tmA;  // unused by the push epilogue
+  }
   GemmParams p{};
   p.M = a.M; p.N = a.N; p.K = a.K;
   p.m_tiles = (a.M + BM - 1) / BM;
@@ -61,7 +70,7 @@ int launch_gemm_t(const GemmArgs& a) {
   p.splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
   p.D = a.D; p.ldd = a.ldd;
   p.bias = a.bias;
-  p.aux = reinterpret_cast<const __nv_bfloat16*>(a.aux); p.ldaux = a.ldaux;
+  p.mask_in = a.mask_in; p.mask_out = a.mask_out; p.ldmask = a.ldmask;
   p.row_src = a.row_src;
   p.dense_x = reinterpret_cast<const __nv_bfloat16*>(a.dense_x);
   p.a_buf = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(a.A));
@@ -73,7 +82,7 @@ int launch_gemm_t(const GemmArgs& a) {
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of idle CTAs still pull rows
   const int threads = GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads;
-  kern<<<grid, threads, S::kTotal, a.stream>>>(tmA, tmB, p);
+  kern<<<grid, threads, S::kTotal, a.stream>>>(tmA, tmB, tmD, p);
   DTF_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;

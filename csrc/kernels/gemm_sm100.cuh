@@ -31,7 +31,7 @@ enum Epilogue : int {
   EPI_BF16 = 0,            // D = bf16(acc)
   EPI_BIAS_BF16 = 1,       // D = bf16(acc + bias[n])
   EPI_BIAS_RELU_BF16 = 2,  // D = bf16(relu(acc + bias[n]))
-  EPI_DRELU_BF16 = 3,      // D = bf16(aux[m,n] > 0 ? acc : 0)          (dgrad through ReLU)
+  EPI_DRELU_BF16 = 3,      // D = bf16(mask bit(m,n) ? acc : 0)         (dgrad through ReLU)
   EPI_F32 = 4,             // D = acc (fp32)
   EPI_F32_ATOMIC = 5,      // D += acc (fp32, red.global.add; split-K wgrad)
   EPI_PUSH_ROWS = 6,       // bf16 row segments scattered to per-(m,slot) destination pointers
@@ -43,8 +43,9 @@ struct GemmParams {
   void* D;
   long long ldd;  // elements
   const float* bias;
-  const __nv_bfloat16* aux;
-  long long ldaux;
+  const uint32_t* mask_in;   // EPI_DRELU_BF16: bit j of word [m, n/32] = keep column n
+  uint32_t* mask_out;        // EPI_BIAS_RELU_BF16 (optional): same format, bit = (output > 0)
+  long long ldmask;          // words per row (even)
   // --- fused pull (gather warps): rows of 128 bf16 fetched through row_src pointers ---
   const unsigned long long* row_src;  // [M * slots] global addresses of 256-byte rows (may be peer)
   const __nv_bfloat16* dense_x;       // [M, dense_cols] local bf16 (already zero padded)
@@ -64,9 +65,11 @@ struct GemmSmem {
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 4 : ((BN == 128) ? 6 : 8);
-  static constexpr int kBarBytes = 1024;
+  static constexpr int kStagingPerWarp = 5120;  // 32 rows x 128 B (TMA store) or x 144 B (push)
+  static constexpr int kStagingBytes = 4 * kStagingPerWarp;
+  static constexpr int kBarBytes = 256;
   static constexpr int kBiasBytes = BN * 4 * 2;
-  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kBiasBytes + 1024 /*align*/;
+  static constexpr int kTotal = kStages * kStageBytes + kStagingBytes + kBarBytes + kBiasBytes + 1024 /*align*/;
 };
 
 // tile index -> (m, n, split); n fastest so that concurrently running CTAs share A row-tiles.
@@ -81,22 +84,29 @@ __device__ __forceinline__ void decode_tile(const GemmParams& p, int tile, int& 
 template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
 __global__ void __launch_bounds__(GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const GemmParams p) {
+                  const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
   using S = GemmSmem<BN>;
   constexpr int kStages = S::kStages;
   constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : 2 * BN;  // two accumulator buffers
+  constexpr bool kOutF32 = (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC);
+  constexpr bool kPush = (EPI == EPI_PUSH_ROWS);
+  constexpr int CW = kOutF32 ? 32 : 64;          // output columns per 128-byte staging row
+  constexpr int kPitch = kPush ? 144 : 128;      // staging row pitch (push rows are not swizzled)
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   const uint32_t smem_base = smem_u32(smem);
-  const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
+  const uint32_t staging_base = smem_base + kStages * S::kStageBytes;  // 1024-aligned
+  const uint32_t bar_base = staging_base + S::kStagingBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * kStages + b); };
   auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * kStages + 2 + b); };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kStages * S::kStageBytes + 8 * (2 * kStages + 4));
-  float* bias_smem = reinterpret_cast<float*>(smem + kStages * S::kStageBytes + S::kBarBytes);
+  uint8_t* misc = smem + kStages * S::kStageBytes + S::kStagingBytes;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(misc + 8 * (2 * kStages + 4));
+  int* claimed = reinterpret_cast<int*>(misc + 8 * (2 * kStages + 4) + 8);
+  float* bias_smem = reinterpret_cast<float*>(misc + S::kBarBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -106,6 +116,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if constexpr (!kPush) tma_prefetch_desc(&tmD);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
@@ -207,105 +218,117 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp < 6) {
     // =============================== epilogue ===============================
-    const int q = warp & 3;  // TMEM lane quarter this warp may touch
+    // TMEM -> registers -> (bias / ReLU / mask) -> 128B-swizzled staging rows in SMEM -> TMA store
+    // (or TMA reduce-add for split-K, or per-row bulk copies to peer mailboxes for the fused push).
+    const int q = warp & 3;           // TMEM lane quarter this warp may touch
     const int et = threadIdx.x - 64;  // 0..127 within the epilogue group
+    const uint32_t stg = staging_base + q * S::kStagingPerWarp;
+    const uint32_t my_row_smem = stg + lane * kPitch;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       int m_t, n_t, s_t;
       decode_tile(p, tile, m_t, n_t, s_t);
       const int buf = it & 1;
       const int n0 = n_t * BN;
-      const int row = m_t * BM + q * 32 + lane;
+      const int row0 = m_t * BM + q * 32;
+      const int row = row0 + lane;
       float* bsm = bias_smem + buf * BN;
       if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_RELU_BF16) {
         for (int i = et; i < BN; i += 128) bsm[i] = (n0 + i < p.N) ? __ldg(p.bias + n0 + i) : 0.f;
         named_bar_sync(1, 128);
       }
+      // operands of the epilogue that do not depend on the accumulator are fetched before the wait
+      uint32_t mw[BN / 32];
+      if constexpr (EPI == EPI_DRELU_BF16) {
+#pragma unroll
+        for (int i = 0; i < BN / 32; ++i)
+          mw[i] = (row < p.M && n0 + i * 32 < p.N) ? __ldg(p.mask_in + static_cast<long long>(row) * p.ldmask + (n0 >> 5) + i)
+                                                   : 0u;
+      }
+      unsigned long long pdst[(BN + 127) / 128];
+      if constexpr (kPush) {
+#pragma unroll
+        for (int i = 0; i < (BN + 127) / 128; ++i) {
+          const int f = (n0 >> 7) + i;
+          pdst[i] = (row < p.M && f < p.slots) ? __ldg(p.row_dst + static_cast<long long>(row) * p.slots + f) : 0ull;
+        }
+      }
       mbar_wait(tfull_bar(buf), (it >> 1) & 1);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + c * 32, r);
-        tmem_ld_wait();
-        const int col = n0 + c * 32;
-        if (row < p.M && col < p.N) {
-          const bool full = (col + 32 <= p.N);
-          if constexpr (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC) {
-            float* drow = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + col;
-            if (full && ((reinterpret_cast<uintptr_t>(drow) & 15) == 0)) {
+      for (int c = 0; c < BN / CW; ++c) {
+        uint32_t w[32];  // 128 bytes of output for this thread's row
+        if constexpr (kOutF32) {
+          tmem_ld_32x32(t_row + c * 32, w);
+          tmem_ld_wait();
+        } else {
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32(t_row + c * 64, r0);
+          tmem_ld_32x32(t_row + c * 64 + 32, r1);
+          tmem_ld_wait();
+          float v[64];
 #pragma unroll
-              for (int j = 0; j < 32; j += 4) {
-                if constexpr (EPI == EPI_F32_ATOMIC) {
-                  red_add_f32x4(drow + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                                __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-                } else {
-                  st_global_v4(drow + j, r[j], r[j + 1], r[j + 2], r[j + 3]);
+          for (int j = 0; j < 32; ++j) {
+            v[j] = __uint_as_float(r0[j]);
+            v[32 + j] = __uint_as_float(r1[j]);
+          }
+          if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_RELU_BF16) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) {
+              v[j] += bsm[c * 64 + j];
+              if (EPI == EPI_BIAS_RELU_BF16) v[j] = fmaxf(v[j], 0.f);
+            }
+            if constexpr (EPI == EPI_BIAS_RELU_BF16) {
+              if (p.mask_out != nullptr) {
+                uint32_t m0 = 0, m1 = 0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  m0 |= (v[j] > 0.f ? 1u : 0u) << j;
+                  m1 |= (v[32 + j] > 0.f ? 1u : 0u) << j;
                 }
-              }
-            } else {
-              for (int j = 0; j < 32 && col + j < p.N; ++j) {
-                if constexpr (EPI == EPI_F32_ATOMIC) atomicAdd(drow + j, __uint_as_float(r[j]));
-                else drow[j] = __uint_as_float(r[j]);
-              }
-            }
-          } else {
-            float v[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-            if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_RELU_BF16) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                v[j] += bsm[c * 32 + j];
-                if (EPI == EPI_BIAS_RELU_BF16) v[j] = fmaxf(v[j], 0.f);
+                const int col = n0 + c * 64;
+                if (row < p.M && col < p.N)
+                  *reinterpret_cast<uint2*>(p.mask_out + static_cast<long long>(row) * p.ldmask + (col >> 5)) =
+                      make_uint2(m0, m1);
               }
             }
-            if constexpr (EPI == EPI_DRELU_BF16) {
-              const __nv_bfloat16* arow = p.aux + static_cast<long long>(row) * p.ldaux + col;
-              if (full && ((reinterpret_cast<uintptr_t>(arow) & 15) == 0)) {
+          }
+          if constexpr (EPI == EPI_DRELU_BF16) {
+            const uint32_t m0 = mw[2 * c], m1 = mw[2 * c + 1];
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                  uint4 h = ld_global_nc_v4(arow + j);
-                  const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    // post-ReLU activations are >= 0, so "> 0" is "low 15 bits or high 15 bits set"
-                    if ((hw[e] & 0x7FFFu) == 0u || (hw[e] & 0x8000u)) v[j + 2 * e] = 0.f;
-                    if ((hw[e] & 0x7FFF0000u) == 0u || (hw[e] & 0x80000000u)) v[j + 2 * e + 1] = 0.f;
-                  }
-                }
-              } else {
-                for (int j = 0; j < 32 && col + j < p.N; ++j)
-                  if (!(__bfloat162float(arow[j]) > 0.f)) v[j] = 0.f;
-              }
+            for (int j = 0; j < 32; ++j) {
+              if (!((m0 >> j) & 1u)) v[j] = 0.f;
+              if (!((m1 >> j) & 1u)) v[32 + j] = 0.f;
             }
-            if constexpr (EPI == EPI_PUSH_ROWS) {
-              // 128-wide row of slot f lives behind row_dst[row*slots + f]; this chunk covers
-              // 32 of its columns.
-              const int f = col >> 7;
-              if (f < p.slots) {
-                const unsigned long long dst = p.row_dst[static_cast<long long>(row) * p.slots + f];
-                if (dst != 0ull) {
-                  uint8_t* d8 = reinterpret_cast<uint8_t*>(dst) + (col & 127) * 2;
+          }
 #pragma unroll
-                  for (int j = 0; j < 32; j += 8)
-                    st_global_v4(d8 + j * 2, pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                                 pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-                }
-              }
-            } else {
-              __nv_bfloat16* drow =
-                  reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + col;
-              if (full && ((reinterpret_cast<uintptr_t>(drow) & 15) == 0)) {
+          for (int j = 0; j < 32; ++j) w[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        }
+        // the staging row must have been read out by the previous chunk's bulk operation
+        if constexpr (kPush) {
+          tma_store_wait_read<0>();
+        } else {
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+        }
 #pragma unroll
-                for (int j = 0; j < 32; j += 8)
-                  st_global_v4(drow + j, pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                               pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-              } else {
-                for (int j = 0; j < 32 && col + j < p.N; ++j) drow[j] = __float2bfloat16(v[j]);
-              }
-            }
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t a = kPush ? (my_row_smem + j * 16) : (my_row_smem + ((j ^ (lane & 7)) << 4));
+          st_shared_v4(a, w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+        }
+        fence_proxy_async_smem();
+        if constexpr (kPush) {
+          const int col = n0 + c * 64;
+          const unsigned long long d = pdst[(c * 64) >> 7];
+          if (d != 0ull) bulk_store_1d(reinterpret_cast<uint8_t*>(d) + (col & 127) * 2, my_row_smem, 128);
+          tma_store_commit();
+        } else {
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (EPI == EPI_F32_ATOMIC) tma_reduce_add_2d(&tmD, stg, n0 + c * CW, row0);
+            else tma_store_2d(&tmD, stg, n0 + c * CW, row0);
+            tma_store_commit();
           }
         }
       }
@@ -313,17 +336,17 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(buf));
     }
+    tma_store_wait_all();
   } else {
     // =============================== gather warps (fused pull) ===============================
     if constexpr (GATHER) {
       const int gt = threadIdx.x - kNumMainThreads;  // 0..127
       const int chunks_per_tile = p.slots + 1;
       const int total_chunks = p.m_tiles * chunks_per_tile;
-      __shared__ int claimed;
       for (;;) {
-        if (gt == 0) claimed = static_cast<int>(atomicAdd(p.chunk_counter, 1u));
+        if (gt == 0) *claimed = static_cast<int>(atomicAdd(p.chunk_counter, 1u));
         named_bar_sync(2, kNumGatherThreads);
-        const int chunk = claimed;
+        const int chunk = *claimed;
         named_bar_sync(3, kNumGatherThreads);
         if (chunk >= total_chunks) break;
         const int m_t = chunk / chunks_per_tile;

@@ -34,22 +34,51 @@ def _ld(t: torch.Tensor) -> int:
     return t.stride(0)
 
 
-def gemm_raw(A, a_mn, B, b_mn, D, M, N, K, epilogue, bias=None, aux=None, splits=1, bn=0, stream=None):
+def mask_words(n_cols: int) -> int:
+    """uint32 words per row of a ReLU bit-mask covering ``n_cols`` columns (even, for 8-byte stores)."""
+    w = (n_cols + 31) // 32
+    return w + (w & 1)
+
+
+def pack_mask(keep: torch.Tensor) -> torch.Tensor:
+    """Pack a boolean [M, N] matrix into the int32 bit-mask layout of the GEMM epilogues (host helper
+    for tests; the forward kernel writes this layout itself)."""
+    M, N = keep.shape
+    W = mask_words(N)
+    pad = torch.zeros(M, W * 32, dtype=torch.int64, device=keep.device)
+    pad[:, :N] = keep.to(torch.int64)
+    weights = (1 << torch.arange(32, device=keep.device, dtype=torch.int64))
+    words = (pad.view(M, W, 32) * weights).sum(-1)
+    words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)
+    return words.to(torch.int32).contiguous()
+
+
+def unpack_mask(mask: torch.Tensor, n_cols: int) -> torch.Tensor:
+    M, W = mask.shape
+    bits = (mask.to(torch.int64).unsqueeze(-1) >> torch.arange(32, device=mask.device)) & 1
+    return bits.view(M, W * 32)[:, :n_cols].bool()
+
+
+def gemm_raw(A, a_mn, B, b_mn, D, M, N, K, epilogue, bias=None, mask_in=None, mask_out=None, splits=1, bn=0,
+             stream=None):
     L = _lib.lib()
     rc = L.dtf_gemm_bf16(
         _lib.ptr(A), ctypes.c_longlong(_ld(A)), ctypes.c_int(int(a_mn)),
         _lib.ptr(B), ctypes.c_longlong(_ld(B)), ctypes.c_int(int(b_mn)),
         _lib.ptr(D), ctypes.c_longlong(_ld(D)),
         ctypes.c_int(M), ctypes.c_int(N), ctypes.c_int(K), ctypes.c_int(epilogue),
-        _lib.ptr(bias), _lib.ptr(aux), ctypes.c_longlong(_ld(aux) if aux is not None else 0),
+        _lib.ptr(bias), _lib.ptr(mask_in), _lib.ptr(mask_out),
+        ctypes.c_longlong(_ld(mask_in) if mask_in is not None else (_ld(mask_out) if mask_out is not None else 0)),
         ctypes.c_int(splits), ctypes.c_int(bn), _lib.stream_ptr(stream))
     _lib.check(rc, "dtf_gemm_bf16")
     return D
 
 
 def linear_fw(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, relu: bool = False,
-              out: torch.Tensor | None = None, out_dtype=torch.bfloat16, bn: int = 0) -> torch.Tensor:
-    """``act(x @ w.T + bias)``; x [M,K] bf16, w [N,K] bf16, bias [N] fp32."""
+              out: torch.Tensor | None = None, out_dtype=torch.bfloat16, bn: int = 0,
+              mask_out: torch.Tensor | None = None) -> torch.Tensor:
+    """``act(x @ w.T + bias)``; x [M,K] bf16, w [N,K] bf16, bias [N] fp32.  With ``relu`` and
+    ``mask_out`` (int32 [M, mask_words(N)]) the kernel also records which outputs are > 0."""
     M, K = x.shape
     N = w.shape[0]
     assert w.shape[1] == K and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
@@ -63,21 +92,21 @@ def linear_fw(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None
     else:
         assert not relu
         epi = EPI_BF16
-    return gemm_raw(x, 0, w, 0, out, M, N, K, epi, bias=bias, bn=bn)
+    return gemm_raw(x, 0, w, 0, out, M, N, K, epi, bias=bias, mask_out=mask_out if relu else None, bn=bn)
 
 
-def linear_dx(dy: torch.Tensor, w: torch.Tensor, h_in: torch.Tensor | None = None,
+def linear_dx(dy: torch.Tensor, w: torch.Tensor, mask: torch.Tensor | None = None,
               out: torch.Tensor | None = None, bn: int = 0) -> torch.Tensor:
-    """``(dy @ w) * (h_in > 0)``; dy [M,N] bf16, w [N,K] bf16, h_in [M,K] bf16 (the post-ReLU input
-    activation of this layer, i.e. the mask of the previous layer) or None for no mask."""
+    """``(dy @ w) * mask``; dy [M,N] bf16, w [N,K] bf16, mask = ReLU bit-mask [M, mask_words(K)] int32
+    recorded by the forward of the layer that produced this layer's input (None = no mask)."""
     M, N = dy.shape
     K = w.shape[1]
     assert w.shape[0] == N
     if out is None:
         out = torch.empty(M, K, device=dy.device, dtype=torch.bfloat16)
-    epi = EPI_DRELU_BF16 if h_in is not None else EPI_BF16
+    epi = EPI_DRELU_BF16 if mask is not None else EPI_BF16
     # GEMM view: D[M, K] = dy[M, N] * (w^T)[K, N]^T ; reduction over N; w is stored [N(red), K] = MN-major
-    return gemm_raw(dy, 0, w, 1, out, M, K, N, epi, aux=h_in, bn=bn)
+    return gemm_raw(dy, 0, w, 1, out, M, K, N, epi, mask_in=mask, bn=bn)
 
 
 def linear_dw(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = False,

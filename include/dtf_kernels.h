@@ -28,7 +28,7 @@ enum {
   DTF_EPI_BF16 = 0,           /* D = bf16(acc)                                  */
   DTF_EPI_BIAS_BF16 = 1,      /* D = bf16(acc + bias[n])                        */
   DTF_EPI_BIAS_RELU_BF16 = 2, /* D = bf16(max(acc + bias[n], 0))                */
-  DTF_EPI_DRELU_BF16 = 3,     /* D = bf16(aux[m,n] > 0 ? acc : 0)               */
+  DTF_EPI_DRELU_BF16 = 3,     /* D = bf16(mask bit(m,n) ? acc : 0)              */
   DTF_EPI_F32 = 4,            /* D = acc (fp32)                                 */
   DTF_EPI_F32_ATOMIC = 5      /* D += acc (fp32 red.global.add; for split-K)    */
 };
@@ -39,11 +39,16 @@ enum {
  * Supported layouts: (0,0) forward, (0,1) data gradient, (1,1) weight gradient.
  * Row strides must be multiples of 8 elements and bases 16-byte aligned (TMA).
  * splits > 1 partitions K across CTAs and requires DTF_EPI_F32_ATOMIC (D pre-zeroed by caller).
+ * ReLU masks are bit matrices: uint32 word [m, n/32] bit (n%32); ldmask = words per row, even,
+ *   >= ceil(N/32).  DTF_EPI_BIAS_RELU_BF16 writes one to mask_out when it is non-NULL (bit =
+ *   output > 0); DTF_EPI_DRELU_BF16 reads mask_in.  D must satisfy the same alignment as A/B
+ *   (it is written by TMA stores).
  * bn: N tile (64/128/256) or 0 to let the library choose.
  * Stands in for the Mul/Add/Sum Eigen kernels behind reference trainer/task.py:137-139. */
 int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn,
                   void* D, long long ldd, int M, int N, int K, int epilogue, const float* bias,
-                  const void* aux, long long ldaux, int splits, int bn, void* stream);
+                  const void* mask_in, void* mask_out, long long ldmask, int splits, int bn,
+                  void* stream);
 
 #ifdef __cplusplus
 }
