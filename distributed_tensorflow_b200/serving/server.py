@@ -1,0 +1,140 @@
+"""JSON-over-HTTP predict endpoint for exported models (README.md:29-41 of the reference).
+
+The reference serves its SavedModel with the external ``simple_tensorflow_serving`` tool::
+
+    simple_tensorflow_serving --port=8500 --model_base_path="./saved_model"
+    curl -H "Content-Type: application/json" -X POST \
+         -d '{"keys": [[11.0], [2.0]], "features": [[1], [2]]}' http://127.0.0.1:8500
+
+This module is that server: it picks the highest-numbered version directory under
+``--model_base_path``, reads the ``serving_default`` signature, feeds the request's top-level keys
+(or the ``{"data": {...}}`` envelope) as signature inputs -- casting to the declared dtypes, so the
+float ``keys`` of the README become int32 -- and answers with the signature outputs as nested lists:
+``{"keys": [[11], [2]], "prediction": [[w+b], [2w+b]]}``.
+
+Run: ``python -m distributed_tensorflow_b200.serving --port=8500 --model_base_path=./saved_model``
+"""
+from __future__ import annotations
+
+import json
+import os
+import threading
+import time
+from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
+from typing import Dict, Optional
+
+import numpy as np
+
+from ..export.saved_model import DEFAULT_SERVING_SIGNATURE_DEF_KEY, load_saved_model
+
+_DT_TO_NP = {1: np.float32, 3: np.int32, 9: np.int64}
+
+
+def latest_version_dir(model_base_path: str) -> str:
+    versions = [d for d in os.listdir(model_base_path)
+                if d.isdigit() and os.path.isdir(os.path.join(model_base_path, d))]
+    if not versions:
+        raise FileNotFoundError("no numeric version directory under %r" % model_base_path)
+    return os.path.join(model_base_path, max(versions, key=int))
+
+
+class ModelServer:
+    """Loaded model + predict(); independent of the HTTP layer so it can be benchmarked directly."""
+
+    def __init__(self, model_base_path: str, signature: str = DEFAULT_SERVING_SIGNATURE_DEF_KEY,
+                 device: str = "auto"):
+        self.model_base_path = model_base_path
+        self.export_dir = latest_version_dir(model_base_path)
+        self.version = int(os.path.basename(self.export_dir))
+        loaded = load_saved_model(self.export_dir)
+        if signature not in loaded["signatures"]:
+            raise KeyError("signature %r not in %s" % (signature, sorted(loaded["signatures"])))
+        self.signature = loaded["signatures"][signature]
+        self.variables: Dict[str, np.ndarray] = loaded["variables"]
+        self.description = loaded["description"] or {}
+        self.input_dtypes = {k: _DT_TO_NP[v.dtype] for k, v in self.signature.inputs.items()}
+        self.output_names = sorted(self.signature.outputs)
+        self.model_name = self.description.get("model", "linear")
+        self._impl = self._build(device)
+        self.requests = 0
+
+    def _build(self, device: str):
+        if self.model_name == "linear":
+            from ..models.linear import LinearModel
+            m = LinearModel()
+            return lambda inputs: m.predict(self.variables, inputs)
+        if self.model_name == "wide_deep":
+            from ..models.wide_deep_serving import WideDeepPredictor
+            p = WideDeepPredictor(self.variables, self.description.get("config", {}), device=device)
+            return p.predict
+        raise ValueError("exported model %r is not servable by this build" % self.model_name)
+
+    def predict(self, request: dict) -> dict:
+        data = request.get("data", request) if isinstance(request, dict) else None
+        if not isinstance(data, dict):
+            raise ValueError("request body must be a JSON object")
+        inputs = {}
+        for alias, dt in self.input_dtypes.items():
+            if alias not in data:
+                raise ValueError("missing input %r (signature inputs: %s)" % (alias, sorted(self.input_dtypes)))
+            inputs[alias] = np.asarray(data[alias]).astype(dt)
+        n = {v.shape[0] for v in inputs.values() if v.ndim > 0}
+        if len(n) > 1:
+            raise ValueError("inputs disagree on batch size: %s" % sorted(n))
+        out = self._impl(inputs)
+        self.requests += 1
+        return {k: np.asarray(out[k]).tolist() for k in self.output_names}
+
+
+def make_http_server(model: ModelServer, host: str = "0.0.0.0", port: int = 8500) -> ThreadingHTTPServer:
+    class Handler(BaseHTTPRequestHandler):
+        protocol_version = "HTTP/1.1"
+
+        def _send(self, code: int, payload: dict) -> None:
+            body = json.dumps(payload).encode()
+            self.send_response(code)
+            self.send_header("Content-Type", "application/json")
+            self.send_header("Content-Length", str(len(body)))
+            self.end_headers()
+            self.wfile.write(body)
+
+        def do_GET(self):  # noqa: N802  (health / model info)
+            self._send(200, {"model": model.model_name, "version": model.version,
+                             "signature_inputs": sorted(model.input_dtypes), "signature_outputs": model.output_names,
+                             "requests": model.requests})
+
+        def do_POST(self):  # noqa: N802
+            try:
+                n = int(self.headers.get("Content-Length", "0"))
+                req = json.loads(self.rfile.read(n) or b"{}")
+                self._send(200, model.predict(req))
+            except (ValueError, KeyError, TypeError) as e:
+                self._send(400, {"error": str(e)})
+            except Exception as e:  # pragma: no cover
+                self._send(500, {"error": "%s: %s" % (type(e).__name__, e)})
+
+        def log_message(self, fmt, *args):
+            pass
+
+    return ThreadingHTTPServer((host, port), Handler)
+
+
+def main(argv=None) -> int:
+    import argparse
+    ap = argparse.ArgumentParser(description="JSON predict server for exported models")
+    ap.add_argument("--port", type=int, default=8500)
+    ap.add_argument("--host", default="0.0.0.0")
+    ap.add_argument("--model_base_path", default="./saved_model")
+    ap.add_argument("--device", default="auto")
+    args = ap.parse_args(argv)
+    ms = ModelServer(args.model_base_path, device=args.device)
+    httpd = make_http_server(ms, args.host, args.port)
+    print("Serving model %s version %d from %s on port %d" % (ms.model_name, ms.version, ms.export_dir, args.port),
+          flush=True)
+    try:
+        httpd.serve_forever()
+    except KeyboardInterrupt:
+        pass
+    finally:
+        httpd.server_close()
+    return 0

@@ -135,8 +135,9 @@ int dtfn_client_assign_add_i64(dtfn_client*, const char* name, long long delta, 
 int dtfn_client_queue_create(dtfn_client*, const char* name, int capacity);
 int dtfn_client_enqueue(dtfn_client*, const char* name, int value);
 int dtfn_client_dequeue(dtfn_client*, const char* name, int* value, int timeout_ms);  /* -2 on timeout */
-/* ask the server to write all its variables as a single-shard bundle at prefix (ps-side SaveV2) */
-int dtfn_client_save(dtfn_client*, const char* prefix);
+/* ask the server to write its variables as a single-shard bundle at prefix (ps-side SaveV2);
+ * names listed in the '\n'-joined exclude string (may be NULL) are skipped */
+int dtfn_client_save(dtfn_client*, const char* prefix, const char* exclude_newline_joined);
 int dtfn_client_shutdown_server(dtfn_client*);
 
 #ifdef __cplusplus
