@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import os
 import re
+import threading
 import time
 import uuid
 from typing import Dict, List, Optional
@@ -133,6 +134,7 @@ class Saver:
         self.var_list = list(var_list) if var_list is not None else None
         self.sharded, self.max_to_keep, self.write_meta_graph = sharded, max_to_keep, write_meta_graph
         self._last_checkpoints: List[str] = []
+        self._lock = threading.Lock()   # the Supervisor's timer thread and the trainer may both save
 
     @property
     def last_checkpoints(self) -> List[str]:
@@ -149,6 +151,10 @@ class Saver:
         return {k: v for k, v in tensors.items() if k in self.var_list}
 
     def save(self, store, save_path: str, global_step: Optional[int] = None, write_state: bool = True) -> str:
+        with self._lock:
+            return self._save(store, save_path, global_step, write_state)
+
+    def _save(self, store, save_path: str, global_step: Optional[int], write_state: bool) -> str:
         prefix = save_path if global_step is None else "%s-%d" % (save_path, int(global_step))
         save_dir = os.path.dirname(prefix) or "."
         os.makedirs(save_dir, exist_ok=True)

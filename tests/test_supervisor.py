@@ -1,0 +1,132 @@
+"""Supervisor semantics (reference trainer/task.py:215-226): chief restore-or-init,
+non-chief wait, immediate first checkpoint then periodic, no forced save at exit, exceptions
+re-raised by managed_session."""
+import os
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from distributed_tensorflow_b200.checkpoint.saver import Saver, latest_checkpoint
+from distributed_tensorflow_b200.cluster import ClusterSpec, Server
+from distributed_tensorflow_b200.models.linear import LinearModel
+from distributed_tensorflow_b200.optim import get_optimizer
+from distributed_tensorflow_b200.session import LocalSession, PSSession
+from distributed_tensorflow_b200.summary import read_events
+from distributed_tensorflow_b200.supervisor import Coordinator, LooperThread, OutOfRangeError, Supervisor
+
+
+def _local_factory():
+    model = LinearModel()
+    return lambda target: LocalSession(model, get_optimizer("adagrad", 0.1))
+
+
+def test_chief_inits_saves_immediately_then_periodically_and_not_at_exit(tmp_path):
+    d = str(tmp_path / "ckpt")
+    sv = Supervisor(is_chief=True, logdir=d, saver=Saver(), global_step="global_step", save_model_secs=0.3,
+                    save_summaries_secs=0.2, session_factory=_local_factory())
+    with sv.managed_session("") as sess:
+        assert sess.is_ready() and sess.global_step() == 0
+        time.sleep(0.15)
+        assert os.path.exists(os.path.join(d, "model.ckpt-0.index"))            # first save is immediate
+        for _ in range(7):
+            sess.train_step(np.array([[0.5]]), np.array([[11.0]]))
+        time.sleep(0.45)
+        assert os.path.exists(os.path.join(d, "model.ckpt-7.index"))            # timer tick
+        for _ in range(3):
+            sess.train_step(np.array([[0.5]]), np.array([[11.0]]))
+    assert not os.path.exists(os.path.join(d, "model.ckpt-10.index"))           # no final save
+    assert os.path.exists(os.path.join(d, "graph.pbtxt"))
+    assert sv.restored_from is None
+    ev = [f for f in os.listdir(d) if f.startswith("events.out.tfevents")]
+    tags = {t for e in read_events(os.path.join(d, ev[0])) for t in e.get("summary", {})}
+    assert tags == {"global_step/sec"}
+
+
+def test_chief_restart_restores_latest_checkpoint_including_slots(tmp_path):
+    d = str(tmp_path / "ckpt")
+    sv = Supervisor(is_chief=True, logdir=d, saver=Saver(), global_step="global_step", save_model_secs=1000,
+                    session_factory=_local_factory())
+    with sv.managed_session("") as sess:
+        while not os.path.exists(os.path.join(d, "checkpoint")):               # let the immediate save land
+            time.sleep(0.01)
+        for _ in range(5):
+            sess.train_step(np.array([[0.5]]), np.array([[11.0]]))
+        sv.saver.save(sess, sv.save_path, global_step=sess.global_step())
+        w, acc = float(sess.value("weight")), float(sess.value("weight/Adagrad"))
+    sv2 = Supervisor(is_chief=True, logdir=d, saver=Saver(), global_step="global_step", save_model_secs=1000,
+                     session_factory=_local_factory())
+    with sv2.managed_session("") as sess:
+        assert sv2.restored_from == os.path.join(d, "model.ckpt-5")
+        assert sess.global_step() == 5
+        assert float(sess.value("weight")) == w and float(sess.value("weight/Adagrad")) == acc
+
+
+def test_non_chief_waits_until_chief_has_initialised():
+    srv = Server(ClusterSpec({"ps": ["127.0.0.1:0"]}), "ps", 0)
+    cluster = ClusterSpec({"ps": ["127.0.0.1:%d" % srv.port]})
+    model = LinearModel()
+    factory = lambda target: PSSession(model, get_optimizer("sgd", 0.01), cluster, connect_retry_secs=1)
+    try:
+        worker = Supervisor(is_chief=False, logdir=None, saver=None, global_step="global_step",
+                            recovery_wait_secs=0.05, session_factory=factory)
+        got = {}
+
+        def run_worker():
+            with worker.managed_session("") as s:
+                got["step"] = s.global_step()
+        t = threading.Thread(target=run_worker)
+        t.start()
+        time.sleep(0.3)
+        assert t.is_alive() and "step" not in got                                # still polling
+        chief = Supervisor(is_chief=True, logdir=None, saver=None, global_step="global_step",
+                           session_factory=factory)
+        with chief.managed_session("") as s:
+            t.join(5)
+            assert got == {"step": 0}
+        with pytest.raises(RuntimeError):
+            worker.start_standard_services(None)
+    finally:
+        srv.stop()
+
+
+def test_non_chief_gives_up_after_max_wait():
+    srv = Server(ClusterSpec({"ps": ["127.0.0.1:0"]}), "ps", 0)
+    cluster = ClusterSpec({"ps": ["127.0.0.1:%d" % srv.port]})
+    try:
+        sv = Supervisor(is_chief=False, recovery_wait_secs=0.05, max_wait_secs=0.2, saver=None,
+                        session_factory=lambda t: PSSession(LinearModel(), None, cluster, connect_retry_secs=1))
+        with pytest.raises(TimeoutError):
+            with sv.managed_session(""):
+                pass
+    finally:
+        srv.stop()
+
+
+def test_managed_session_reraises_but_swallows_out_of_range(tmp_path):
+    sv = Supervisor(is_chief=True, logdir=str(tmp_path), saver=Saver(), global_step="global_step",
+                    save_model_secs=1000, session_factory=_local_factory())
+    with pytest.raises(ZeroDivisionError):
+        with sv.managed_session(""):
+            1 / 0
+    assert sv.should_stop()
+    with sv.managed_session(""):
+        raise OutOfRangeError()
+
+
+def test_coordinator_and_looper():
+    coord = Coordinator()
+    ticks = []
+    t = LooperThread(coord, 0.02, target=lambda: ticks.append(time.time()))
+    t.start()
+    time.sleep(0.15)
+    coord.request_stop()
+    coord.join()
+    assert len(ticks) >= 3 and not t.is_alive()
+    coord.clear_stop()
+    bad = LooperThread(coord, 0.01, target=lambda: 1 / 0)
+    bad.start()
+    assert coord.wait_for_stop(2)
+    with pytest.raises(ZeroDivisionError):
+        coord.join()
