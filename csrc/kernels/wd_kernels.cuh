@@ -1,0 +1,526 @@
+// Device kernels of the wide-and-deep step that are not GEMMs: routing, loss / last layer / wide
+// part, bias-gradient column sums, the parameter-server side applies (sparse scatter-add and dense
+// reduce-scatter fused with SGD / Adagrad / Adam) and the cross-rank barrier.
+//
+// Reference call sites being replaced: variable reads and Apply* ops on the ps behind
+// optimizer.minimize(loss, global_step) (reference trainer/task.py:137-139), use_locking=False
+// (async) plus the sync-replica mode required by the north star.
+#pragma once
+
+#include "sm100_ptx.cuh"
+#include "wd.cuh"
+
+namespace dtf {
+
+// ------------------------------------------------------------------------------------------ utils
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__device__ __forceinline__ float uniform_pm1(uint64_t key) {  // (-1, 1)
+  return (static_cast<float>(splitmix64(key) >> 40) + 0.5f) * (2.0f / 16777216.0f) - 1.0f;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+struct OptConst {
+  float lr;       // SGD / Adagrad step; for Adam: lr * sqrt(1 - b2^t) / (1 - b1^t)
+  float beta1, beta2, eps;
+};
+
+template <int OPT>
+__device__ __forceinline__ void opt_update(float& w, float g, float& s1, float& s2, const OptConst& c) {
+  if (OPT == WD_SGD) {
+    w -= c.lr * g;
+  } else if (OPT == WD_ADAGRAD) {
+    s1 += g * g;
+    w -= c.lr * g * rsqrtf(s1);
+  } else {
+    s1 = c.beta1 * s1 + (1.f - c.beta1) * g;
+    s2 = c.beta2 * s2 + (1.f - c.beta2) * g * g;
+    w -= c.lr * s1 / (sqrtf(s2) + c.eps);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ init
+__global__ void wd_init_embedding_kernel(float* __restrict__ master, __nv_bfloat16* __restrict__ work,
+                                         float* __restrict__ slot1, float* __restrict__ slot2,
+                                         float* __restrict__ wide, float* __restrict__ wide_s1,
+                                         float* __restrict__ wide_s2, long long rows_local, int world, int rank,
+                                         unsigned long long seed, float scale, float slot1_init) {
+  const long long n = rows_local * kEmbDim;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long lrow = i / kEmbDim;
+    const int col = static_cast<int>(i % kEmbDim);
+    const unsigned long long grow = static_cast<unsigned long long>(lrow) * world + rank;
+    const float v = scale * uniform_pm1(seed ^ (grow * 131ull + col));
+    master[i] = v;
+    work[i] = __float2bfloat16(v);
+    if (slot1) slot1[i] = slot1_init;
+    if (slot2) slot2[i] = 0.f;
+    if (col == 0) {
+      wide[lrow] = 0.f;  // TF's linear (wide) columns start at zero
+      if (wide_s1) wide_s1[lrow] = slot1_init;
+      if (wide_s2) wide_s2[lrow] = 0.f;
+    }
+  }
+}
+
+__global__ void wd_init_dense_kernel(float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2,
+                                     long long lo, long long hi, DenseLayout dl, WdShapes sh, unsigned long long seed,
+                                     float slot1_init) {
+  for (long long i = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float fan_in = 0.f;
+    if (i < dl.w2) fan_in = static_cast<float>(sh.K0);
+    else if (i < dl.w3) fan_in = static_cast<float>(sh.h1);
+    else if (i < dl.small_begin) fan_in = static_cast<float>(sh.h2);
+    else if (i >= dl.w4 && i < dl.w4 + sh.h3) fan_in = static_cast<float>(sh.h3);
+    float v = 0.f;
+    if (fan_in > 0.f) v = rsqrtf(fan_in) * uniform_pm1((seed * 0x51ull) ^ static_cast<unsigned long long>(i));
+    // padding between segments stays zero
+    const bool in_w1 = i < dl.w1 + static_cast<long long>(sh.h1) * sh.K0;
+    const bool in_w2 = i >= dl.w2 && i < dl.w2 + static_cast<long long>(sh.h2) * sh.h1;
+    const bool in_w3 = i >= dl.w3 && i < dl.w3 + static_cast<long long>(sh.h3) * sh.h2;
+    const bool in_w4 = i >= dl.w4 && i < dl.w4 + sh.h3;
+    if (!(in_w1 || in_w2 || in_w3 || in_w4)) v = 0.f;
+    master[i - lo] = v;
+    if (s1) s1[i - lo] = slot1_init;
+    if (s2) s2[i - lo] = 0.f;
+  }
+}
+
+// owner -> every peer: bf16 working copy (+ fp32 copy of the small tail)
+__global__ void wd_dense_broadcast_kernel(const float* __restrict__ master, long long lo, long long hi, PeerTable pt,
+                                          SlabLayout sl, long long small_begin) {
+  for (long long i = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float v = master[i - lo];
+    const __nv_bfloat16 b = __float2bfloat16(v);
+    for (int r = 0; r < pt.world; ++r) {
+      reinterpret_cast<__nv_bfloat16*>(pt.slab[r] + sl.wbf16)[i] = b;
+      if (i >= small_begin) reinterpret_cast<float*>(pt.slab[r] + sl.small_f32)[i - small_begin] = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ route
+// For every (example, slot): where to pull the embedding / wide weight from, and which mailbox entry
+// at the owning shard receives this example's gradient.  Mailbox slots are claimed with one global
+// atomic per (block, owner).
+__global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V, PeerTable pt, SlabLayout sl,
+                                long long cap, unsigned int* __restrict__ cnt,
+                                unsigned long long* __restrict__ row_src, unsigned long long* __restrict__ wide_src,
+                                unsigned long long* __restrict__ row_dst, unsigned long long* __restrict__ dl_dst) {
+  __shared__ unsigned int s_cnt[kMaxWorld];
+  __shared__ unsigned int s_base[kMaxWorld];
+  if (threadIdx.x < kMaxWorld) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  int owner = 0;
+  long long lrow = 0;
+  unsigned int my = 0;
+  if (e < n) {
+    long long id = ids[e];
+    id %= V;
+    if (id < 0) id += V;
+    owner = static_cast<int>(id % pt.world);
+    lrow = id / pt.world;
+    my = atomicAdd(&s_cnt[owner], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < pt.world && s_cnt[threadIdx.x] > 0)
+    s_base[threadIdx.x] = atomicAdd(&cnt[threadIdx.x], s_cnt[threadIdx.x]);
+  __syncthreads();
+  if (e < n) {
+    const unsigned long long entry = static_cast<unsigned long long>(pt.rank) * cap + s_base[owner] + my;
+    uint8_t* oslab = pt.slab[owner];
+    row_src[e] = reinterpret_cast<unsigned long long>(oslab + sl.emb_bf16) + static_cast<unsigned long long>(lrow) * (kEmbDim * 2);
+    wide_src[e] = reinterpret_cast<unsigned long long>(oslab + sl.wide) + static_cast<unsigned long long>(lrow) * 4;
+    row_dst[e] = reinterpret_cast<unsigned long long>(oslab + sl.mbx_payload) + entry * (kEmbDim * 2);
+    dl_dst[e] = reinterpret_cast<unsigned long long>(oslab + sl.mbx_dl) + entry * 4;
+    reinterpret_cast<int*>(oslab + sl.mbx_rows)[entry] = static_cast<int>(lrow);
+  }
+}
+
+__global__ void wd_dense_pad_kernel(const float* __restrict__ raw, __nv_bfloat16* __restrict__ out, int B, int dense_in,
+                                    int dense_pad) {
+  const int n = B * dense_pad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int m = i / dense_pad, c = i % dense_pad;
+    out[i] = __float2bfloat16(c < dense_in ? raw[m * dense_in + c] : 0.f);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ loss
+// One warp per example: wide gather-sum over the owning shards (P2P loads), last layer h3 . w4,
+// sigmoid cross-entropy, dlogit; then (training) the wide gradient is written straight into the
+// owners' mailboxes, dZ3 = dlogit * w4 masked by ReLU'(h3), and block-reduced gradients of w4 / b4 /
+// wide bias.  SURVEY.md 2E rows K5, K6.
+template <bool TRAIN>
+__global__ void __launch_bounds__(256)
+wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict__ mask3, long long ldmask,
+               const float* __restrict__ small, int off_w4, int off_b4, int off_wide_b,
+               const unsigned long long* __restrict__ wide_src, const unsigned long long* __restrict__ dl_dst,
+               const float* __restrict__ labels, int B, int F, int H3, float inv_batch,
+               float* __restrict__ dlogit, __nv_bfloat16* __restrict__ dz3, float* __restrict__ g_small,
+               float* __restrict__ loss_acc, float* __restrict__ prob_out) {
+  extern __shared__ float s_red[];  // [8][H3 + 2] (train only)
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int chunks = H3 / 256;  // 8 elements per lane per chunk
+  float gw4[4][8];
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) gw4[c][j] = 0.f;
+  float g_b = 0.f, loss_sum = 0.f;
+
+  for (int m = blockIdx.x * (blockDim.x >> 5) + warp; m < B; m += nwarps) {
+    float wide = 0.f;
+    for (int f = lane; f < F; f += 32) {
+      const float* p = reinterpret_cast<const float*>(wide_src[static_cast<long long>(m) * F + f]);
+      float v;
+      asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(v) : "l"(p));
+      wide += v;
+    }
+    float dot = 0.f;
+    float hv[4][8];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      if (c < chunks) {
+        const int col = c * 256 + lane * 8;
+        const uint4 raw = *reinterpret_cast<const uint4*>(h3 + static_cast<long long>(m) * H3 + col);
+        const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f2 = __bfloat1622float2(hp[j]);
+          hv[c][2 * j] = f2.x;
+          hv[c][2 * j + 1] = f2.y;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dot += hv[c][j] * small[off_w4 + col + j];
+      }
+    }
+    dot = warp_sum(dot);
+    wide = warp_sum(wide);
+    const float logit = dot + small[off_b4] + wide + small[off_wide_b];
+    const float p = 1.f / (1.f + __expf(-logit));
+    if (!TRAIN) {
+      if (lane == 0) prob_out[m] = p;
+      continue;
+    }
+    const float y = labels[m];
+    const float dl = (p - y) * inv_batch;
+    if (lane == 0) {
+      dlogit[m] = dl;
+      loss_sum += fmaxf(logit, 0.f) - logit * y + log1pf(__expf(-fabsf(logit)));
+      g_b += dl;
+    }
+    for (int f = lane; f < F; f += 32)
+      *reinterpret_cast<float*>(dl_dst[static_cast<long long>(m) * F + f]) = dl;  // wide gradient push
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      if (c < chunks) {
+        const int col = c * 256 + lane * 8;
+        const uint32_t mword = mask3[static_cast<long long>(m) * ldmask + (col >> 5)];
+        const uint32_t bits = (mword >> (col & 31)) & 0xFFu;
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          gw4[c][j] += dl * hv[c][j];
+          o[j] = ((bits >> j) & 1u) ? dl * small[off_w4 + col + j] : 0.f;
+        }
+        uint4 packed;
+        packed.x = pack_bf16x2(o[0], o[1]);
+        packed.y = pack_bf16x2(o[2], o[3]);
+        packed.z = pack_bf16x2(o[4], o[5]);
+        packed.w = pack_bf16x2(o[6], o[7]);
+        *reinterpret_cast<uint4*>(dz3 + static_cast<long long>(m) * H3 + col) = packed;
+      }
+    }
+  }
+  if (!TRAIN) return;
+  // block reduction of the w4 / b4 / loss partials, one atomic per column per block
+  float* mine = s_red + warp * (H3 + 2);
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+    if (c < chunks)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) mine[c * 256 + lane * 8 + j] = gw4[c][j];
+  if (lane == 0) {
+    mine[H3] = g_b;
+    mine[H3 + 1] = loss_sum;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < H3 + 2; i += blockDim.x) {
+    float s = 0.f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) s += s_red[w * (H3 + 2) + i];
+    if (i < H3) atomicAdd(g_small + off_w4 + i, s);
+    else if (i == H3) {
+      atomicAdd(g_small + off_b4, s);
+      atomicAdd(g_small + off_wide_b, s);
+    } else atomicAdd(loss_acc, s);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ colsum
+// out[n] += sum_m x[m, n]  (bias gradients).  Block = 64 columns x `rows_per_block` rows.
+__global__ void __launch_bounds__(256)
+wd_colsum_kernel(const __nv_bfloat16* __restrict__ x, int M, int N, long long ld, int rows_per_block,
+                 float* __restrict__ out) {
+  __shared__ float s[8][64];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 64 + lane * 2;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(M, r0 + rows_per_block);
+  float a = 0.f, b = 0.f;
+  if (col < N) {
+    for (int r = r0 + warp; r < r1; r += 8) {
+      const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(x + static_cast<long long>(r) * ld + col);
+      const float2 f = __bfloat1622float2(v);
+      a += f.x;
+      b += f.y;
+    }
+  }
+  s[warp][lane * 2] = a;
+  s[warp][lane * 2 + 1] = b;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s[w][threadIdx.x];
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c < N) atomicAdd(out + c, t);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ sparse
+// Mailbox entries of all sources, flattened: entry g belongs to source s with prefix[s] <= g < prefix[s+1].
+struct MailboxView {
+  const __nv_bfloat16* payload;  // [world, cap, 128]
+  const int* rows;               // [world, cap]
+  const float* dl;               // [world, cap]
+  const unsigned int* count;     // [world]
+  long long cap;
+  int world;
+};
+
+__device__ __forceinline__ bool mailbox_locate(const MailboxView& mv, const unsigned int* s_prefix, long long g,
+                                               long long& entry) {
+  int s = 0;
+  while (s < mv.world && g >= s_prefix[s + 1]) ++s;
+  if (s >= mv.world) return false;
+  entry = static_cast<long long>(s) * mv.cap + (g - s_prefix[s]);
+  return true;
+}
+
+// sync-replica, pass 1: G[row] += grad (local fp32 reductions), mark the row as touched
+__global__ void __launch_bounds__(256)
+wd_sparse_accum_kernel(MailboxView mv, float* __restrict__ G, float* __restrict__ wide_G,
+                       unsigned int* __restrict__ bitmap) {
+  __shared__ unsigned int s_prefix[kMaxWorld + 1];
+  if (threadIdx.x == 0) {
+    unsigned int acc = 0;
+    for (int s = 0; s < mv.world; ++s) {
+      s_prefix[s] = acc;
+      acc += min(mv.count[s], static_cast<unsigned int>(mv.cap));
+    }
+    for (int s = mv.world; s <= kMaxWorld; ++s) s_prefix[s] = acc;
+  }
+  __syncthreads();
+  const long long total = s_prefix[mv.world];
+  const int lane = threadIdx.x & 31;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long g = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; g < total; g += nwarps) {
+    long long e;
+    if (!mailbox_locate(mv, s_prefix, g, e)) continue;
+    const int row = mv.rows[e];
+    const uint2 raw = *reinterpret_cast<const uint2*>(mv.payload + e * kEmbDim + lane * 4);
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+    red_add_f32x4(G + static_cast<long long>(row) * kEmbDim + lane * 4, a.x, a.y, b.x, b.y);
+    if (lane == 0) {
+      atomicAdd(wide_G + row, mv.dl[e]);
+      atomicOr(bitmap + (row >> 5), 1u << (row & 31));
+    }
+  }
+}
+
+// sync-replica, pass 2: one optimizer step for every touched row; clears G and the bitmap
+template <int OPT>
+__global__ void __launch_bounds__(256)
+wd_sparse_apply_rows_kernel(unsigned int* __restrict__ bitmap, long long nwords, float* __restrict__ G,
+                            float* __restrict__ wide_G, float* __restrict__ master, float* __restrict__ s1,
+                            float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
+                            float* __restrict__ wide_s1, float* __restrict__ wide_s2, OptConst oc) {
+  const int lane = threadIdx.x & 31;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long wi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; wi < nwords; wi += nwarps) {
+    unsigned int bits = bitmap[wi];
+    if (bits == 0) continue;
+    __syncwarp();
+    if (lane == 0) bitmap[wi] = 0;
+    while (bits) {
+      const int b = __ffs(bits) - 1;
+      bits &= bits - 1;
+      const long long row = wi * 32 + b;
+      const long long o = row * kEmbDim + lane * 4;
+      float4 g = *reinterpret_cast<float4*>(G + o);
+      float4 w = *reinterpret_cast<float4*>(master + o);
+      float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
+      if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + o);
+      if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + o);
+      opt_update<OPT>(w.x, g.x, a.x, v.x, oc);
+      opt_update<OPT>(w.y, g.y, a.y, v.y, oc);
+      opt_update<OPT>(w.z, g.z, a.z, v.z, oc);
+      opt_update<OPT>(w.w, g.w, a.w, v.w, oc);
+      *reinterpret_cast<float4*>(master + o) = w;
+      if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o) = a;
+      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o) = v;
+      *reinterpret_cast<float4*>(G + o) = make_float4(0, 0, 0, 0);
+      uint2 pk;
+      pk.x = pack_bf16x2(w.x, w.y);
+      pk.y = pack_bf16x2(w.z, w.w);
+      *reinterpret_cast<uint2*>(work + o) = pk;
+      if (lane == 0) {
+        float ww = wide[row], wa = 0.f, wv = 0.f;
+        if (OPT != WD_SGD) wa = wide_s1[row];
+        if (OPT == WD_ADAM) wv = wide_s2[row];
+        opt_update<OPT>(ww, wide_G[row], wa, wv, oc);
+        wide[row] = ww;
+        if (OPT != WD_SGD) wide_s1[row] = wa;
+        if (OPT == WD_ADAM) wide_s2[row] = wv;
+        wide_G[row] = 0.f;
+      }
+    }
+  }
+}
+
+// async (Hogwild): every mailbox entry is applied on its own, straight onto the shard, with no
+// duplicate handling and no locks -- concurrent entries for one row race exactly like
+// use_locking=False in the reference's Apply* ops.
+template <int OPT>
+__global__ void __launch_bounds__(256)
+wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float* __restrict__ s1,
+                               float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
+                               float* __restrict__ wide_s1, float* __restrict__ wide_s2, OptConst oc) {
+  __shared__ unsigned int s_prefix[kMaxWorld + 1];
+  if (threadIdx.x == 0) {
+    unsigned int acc = 0;
+    for (int s = 0; s < mv.world; ++s) {
+      s_prefix[s] = acc;
+      acc += min(mv.count[s], static_cast<unsigned int>(mv.cap));
+    }
+    for (int s = mv.world; s <= kMaxWorld; ++s) s_prefix[s] = acc;
+  }
+  __syncthreads();
+  const long long total = s_prefix[mv.world];
+  const int lane = threadIdx.x & 31;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += nwarps) {
+    long long e;
+    if (!mailbox_locate(mv, s_prefix, gi, e)) continue;
+    const long long row = mv.rows[e];
+    const long long o = row * kEmbDim + lane * 4;
+    const uint2 raw = *reinterpret_cast<const uint2*>(mv.payload + e * kEmbDim + lane * 4);
+    const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+    const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+    float4 w = *reinterpret_cast<float4*>(master + o);
+    float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
+    if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + o);
+    if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + o);
+    opt_update<OPT>(w.x, ga.x, a.x, v.x, oc);
+    opt_update<OPT>(w.y, ga.y, a.y, v.y, oc);
+    opt_update<OPT>(w.z, gb.x, a.z, v.z, oc);
+    opt_update<OPT>(w.w, gb.y, a.w, v.w, oc);
+    *reinterpret_cast<float4*>(master + o) = w;
+    if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o) = a;
+    if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o) = v;
+    uint2 pk;
+    pk.x = pack_bf16x2(w.x, w.y);
+    pk.y = pack_bf16x2(w.z, w.w);
+    *reinterpret_cast<uint2*>(work + o) = pk;
+    if (lane == 0) {
+      float ww = wide[row], wa = 0.f, wv = 0.f;
+      if (OPT != WD_SGD) wa = wide_s1[row];
+      if (OPT == WD_ADAM) wv = wide_s2[row];
+      opt_update<OPT>(ww, mv.dl[e], wa, wv, oc);
+      wide[row] = ww;
+      if (OPT != WD_SGD) wide_s1[row] = wa;
+      if (OPT == WD_ADAM) wide_s2[row] = wv;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ dense
+// Owner of [lo, hi): gradient = sum over `nsrc` ranks' gradient buffers read over NVLink
+// (reduce-scatter), optimizer step on the fp32 master + slots, bf16 (and fp32 tail) written into
+// every peer's working copy (all-gather), all in one pass.  SURVEY.md 2E row K2.
+template <int OPT>
+__global__ void __launch_bounds__(256)
+wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, int src_begin, int src_end,
+                      float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2, OptConst oc,
+                      long long small_begin) {
+  const long long n4 = (hi - lo) >> 2;
+  for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < n4;
+       q += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long i = lo + q * 4;
+    float4 g = make_float4(0, 0, 0, 0);
+    for (int r = src_begin; r < src_end; ++r) {
+      const float4 t = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
+      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+    }
+    float4 w = *reinterpret_cast<float4*>(master + (i - lo));
+    float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
+    if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + (i - lo));
+    if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + (i - lo));
+    opt_update<OPT>(w.x, g.x, a.x, v.x, oc);
+    opt_update<OPT>(w.y, g.y, a.y, v.y, oc);
+    opt_update<OPT>(w.z, g.z, a.z, v.z, oc);
+    opt_update<OPT>(w.w, g.w, a.w, v.w, oc);
+    *reinterpret_cast<float4*>(master + (i - lo)) = w;
+    if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + (i - lo)) = a;
+    if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + (i - lo)) = v;
+    uint2 pk;
+    pk.x = pack_bf16x2(w.x, w.y);
+    pk.y = pack_bf16x2(w.z, w.w);
+    for (int r = 0; r < pt.world; ++r) {
+      *reinterpret_cast<uint2*>(pt.slab[r] + sl.wbf16 + i * 2) = pk;
+      if (i >= small_begin) *reinterpret_cast<float4*>(pt.slab[r] + sl.small_f32 + (i - small_begin) * 4) = w;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ barrier
+// Device-side barrier over the signal pads (one 64-byte line per source on every rank).  Thread r
+// optionally publishes how many mailbox entries this rank pushed to rank r, then release-stores
+// `epoch` into rank r's pad and acquire-spins on its own pad until rank r has done the same.
+__global__ void wd_barrier_kernel(PeerTable pt, SlabLayout sl, unsigned int epoch, const unsigned int* publish_cnt) {
+  const int r = threadIdx.x;
+  if (r >= pt.world) return;
+  if (publish_cnt != nullptr) reinterpret_cast<unsigned int*>(pt.slab[r] + sl.mbx_count)[pt.rank] = publish_cnt[r];
+  __threadfence_system();
+  unsigned int* remote = reinterpret_cast<unsigned int*>(pt.slab[r] + sl.signal) + pt.rank * 16;
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+  const unsigned int* mine = reinterpret_cast<const unsigned int*>(pt.slab[pt.rank] + sl.signal) + r * 16;
+  unsigned int v;
+  do {
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+  } while (static_cast<int>(v - epoch) < 0);
+}
+
+// single-rank stand-in for the publish half of the barrier (counts stay local)
+__global__ void wd_publish_local_kernel(PeerTable pt, SlabLayout sl, const unsigned int* publish_cnt) {
+  const int r = threadIdx.x;
+  if (r < pt.world) reinterpret_cast<unsigned int*>(pt.slab[r] + sl.mbx_count)[pt.rank] = publish_cnt[r];
+}
+
+}  // namespace dtf

@@ -1,0 +1,569 @@
+// Host-side executor of the wide-and-deep training / serving step: owns every device buffer, the
+// symmetric slab and the peer table, and launches the whole step (about twenty kernels) from one C
+// call so that Python is not on the critical path.  It plays the part of TensorFlow's C++
+// master/worker executor behind sess.run(train_op) in the reference (reference
+// trainer/task.py:236).
+#include <math.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/dtf_kernels.h"
+#include "gemm_launch.cuh"
+#include "wd_kernels.cuh"
+
+using namespace dtf;
+
+namespace {
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Buf {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+};
+
+}  // namespace
+
+struct dtf_wd_plan {
+  dtf_wd_config cfg{};
+  WdShapes sh{};
+  DenseLayout dl{};
+  SlabLayout sl{};
+  PeerTable pt{};
+  long long P_pad = 0, dense_lo = 0, dense_hi = 0;
+  uint8_t* slab = nullptr;
+  bool owns_slab = true;
+  std::vector<void*> opened;  // IPC mappings to close
+  std::map<std::string, Buf> bufs;
+  std::vector<void*> owned;
+  // local buffers
+  float *emb_master = nullptr, *emb_s1 = nullptr, *emb_s2 = nullptr, *G = nullptr;
+  float *wide_s1 = nullptr, *wide_s2 = nullptr, *wide_G = nullptr;
+  unsigned int* bitmap = nullptr;
+  long long bitmap_words = 0;
+  float *dense_master = nullptr, *dense_s1 = nullptr, *dense_s2 = nullptr;
+  __nv_bfloat16 *a_buf = nullptr, *dense_x = nullptr, *H1 = nullptr, *H2 = nullptr, *H3 = nullptr;
+  __nv_bfloat16 *dZ1 = nullptr, *dZ2 = nullptr, *dZ3 = nullptr;
+  uint32_t *m1 = nullptr, *m2 = nullptr, *m3 = nullptr;
+  int ldm1 = 0, ldm2 = 0, ldm3 = 0;
+  unsigned long long *row_src = nullptr, *wide_src = nullptr, *row_dst = nullptr, *dl_dst = nullptr;
+  float* dlogit = nullptr;
+  float* prob = nullptr;
+  // zeroed at the start of every step: cnt[kMaxWorld] | chunk_counter | pad | loss_acc[2] | tile_flags[m_tiles]
+  unsigned int* zero_region = nullptr;
+  size_t zero_bytes = 0;
+  unsigned int *cnt = nullptr, *chunk_counter = nullptr, *tile_flags = nullptr;
+  float* loss_acc = nullptr;
+  unsigned int epoch = 0;
+  long long step = 0;
+
+  template <typename T>
+  T* alloc(const char* name, size_t count) {
+    void* p = nullptr;
+    const size_t bytes = count * sizeof(T);
+    if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) {
+      set_error("wd plan: cudaMalloc(%zu bytes) for '%s' failed", bytes, name);
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    cudaMemset(p, 0, bytes ? bytes : 16);
+    owned.push_back(p);
+    bufs[name] = Buf{p, bytes};
+    return static_cast<T*>(p);
+  }
+  template <typename T>
+  T* in_slab(const char* name, size_t off, size_t bytes) {
+    bufs[name] = Buf{slab + off, bytes};
+    return reinterpret_cast<T*>(slab + off);
+  }
+};
+
+static int mask_ld(int n) {
+  int w = (n + 31) / 32;
+  return w + (w & 1);
+}
+
+static OptConst opt_const(const dtf_wd_plan* p, long long t) {
+  OptConst oc{};
+  oc.beta1 = 0.9f;
+  oc.beta2 = 0.999f;
+  oc.eps = 1e-8f;
+  oc.lr = p->cfg.lr;
+  if (p->cfg.optimizer == WD_ADAM) {
+    const double b1t = pow(0.9, static_cast<double>(t)), b2t = pow(0.999, static_cast<double>(t));
+    oc.lr = static_cast<float>(p->cfg.lr * sqrt(1.0 - b2t) / (1.0 - b1t));
+  }
+  return oc;
+}
+
+extern "C" {
+
+dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
+  if (cfg->world < 1 || cfg->world > kMaxWorld || cfg->rank < 0 || cfg->rank >= cfg->world) {
+    set_error("wd plan: bad world/rank %d/%d (max world %d)", cfg->world, cfg->rank, kMaxWorld);
+    return nullptr;
+  }
+  if (cfg->emb_dim != kEmbDim) {
+    set_error("wd plan: embedding_dim must be %d (one row = two 128-byte swizzle rows)", kEmbDim);
+    return nullptr;
+  }
+  if (cfg->h3 % 256 != 0 || cfg->h3 > 1024 || cfg->h1 % 64 || cfg->h2 % 64 || cfg->dense_pad % 64 ||
+      cfg->dense_in > cfg->dense_pad || cfg->batch < 1 || cfg->slots < 1) {
+    set_error("wd plan: unsupported shape (h1,h2 multiples of 64; h3 multiple of 256 <= 1024; dense_pad multiple of 64)");
+    return nullptr;
+  }
+  if (cfg->optimizer != WD_SGD && cfg->optimizer != WD_ADAGRAD && cfg->optimizer != WD_ADAM) {
+    set_error("wd plan: optimizer %d not available on the GPU path (sgd=0, adagrad=2, adam=3)", cfg->optimizer);
+    return nullptr;
+  }
+  auto* p = new dtf_wd_plan();
+  p->cfg = *cfg;
+  WdShapes& sh = p->sh;
+  sh.B = cfg->batch; sh.F = cfg->slots; sh.dense_in = cfg->dense_in; sh.dense_pad = cfg->dense_pad;
+  sh.K0 = cfg->slots * kEmbDim + cfg->dense_pad;
+  sh.h1 = cfg->h1; sh.h2 = cfg->h2; sh.h3 = cfg->h3;
+  sh.V = cfg->emb_rows;
+  sh.rows_local = (cfg->emb_rows - cfg->rank + cfg->world - 1) / cfg->world;
+  sh.rows_local_max = (cfg->emb_rows + cfg->world - 1) / cfg->world;
+  sh.cap = static_cast<long long>(cfg->batch) * cfg->slots;
+
+  DenseLayout& dl = p->dl;
+  long long o = 0;
+  dl.w1 = o; o = align_up(o + static_cast<long long>(sh.h1) * sh.K0, 256);
+  dl.w2 = o; o = align_up(o + static_cast<long long>(sh.h2) * sh.h1, 256);
+  dl.w3 = o; o = align_up(o + static_cast<long long>(sh.h3) * sh.h2, 256);
+  dl.small_begin = o;
+  dl.b1 = o; o = align_up(o + sh.h1, 256);
+  dl.b2 = o; o = align_up(o + sh.h2, 256);
+  dl.b3 = o; o = align_up(o + sh.h3, 256);
+  dl.w4 = o; o = align_up(o + sh.h3, 256);
+  dl.b4 = o; o += 4;
+  dl.wide_b = o; o += 4;
+  dl.P = align_up(o, 256);
+  dl.n_small = static_cast<int>(dl.P - dl.small_begin);
+  p->P_pad = align_up(dl.P, 256ll * cfg->world);
+  const long long chunk = p->P_pad / cfg->world;
+  p->dense_lo = chunk * cfg->rank;
+  p->dense_hi = p->dense_lo + chunk;
+
+  SlabLayout& sl = p->sl;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 1024); return r; };
+  sl.emb_bf16 = take(static_cast<size_t>(sh.rows_local_max) * kEmbDim * 2);
+  sl.wide = take(static_cast<size_t>(sh.rows_local_max) * 4);
+  sl.wbf16 = take(static_cast<size_t>(p->P_pad) * 2);
+  sl.small_f32 = take(static_cast<size_t>(dl.n_small + (p->P_pad - dl.P)) * 4);
+  sl.dense_grad = take(static_cast<size_t>(p->P_pad) * 4);
+  sl.mbx_payload = take(static_cast<size_t>(cfg->world) * sh.cap * kEmbDim * 2);
+  sl.mbx_rows = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
+  sl.mbx_dl = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
+  sl.mbx_count = take(kMaxWorld * 4);
+  sl.signal = take(kMaxWorld * 64);
+  sl.total = off;
+
+  void* slab = nullptr;
+  if (dtf_symm_alloc(sl.total, &slab) != 0) {
+    delete p;
+    return nullptr;
+  }
+  p->slab = static_cast<uint8_t*>(slab);
+  p->pt.world = cfg->world;
+  p->pt.rank = cfg->rank;
+  for (int r = 0; r < kMaxWorld; ++r) p->pt.slab[r] = nullptr;
+  p->pt.slab[cfg->rank] = p->slab;
+
+  p->in_slab<void>("emb_bf16", sl.emb_bf16, static_cast<size_t>(sh.rows_local) * kEmbDim * 2);
+  p->in_slab<void>("wide", sl.wide, static_cast<size_t>(sh.rows_local) * 4);
+  p->in_slab<void>("dense_bf16", sl.wbf16, static_cast<size_t>(p->P_pad) * 2);
+  p->in_slab<void>("dense_small_f32", sl.small_f32, static_cast<size_t>(dl.n_small) * 4);
+  p->in_slab<void>("dense_grad", sl.dense_grad, static_cast<size_t>(p->P_pad) * 4);
+  p->in_slab<void>("mbx_payload", sl.mbx_payload, static_cast<size_t>(cfg->world) * sh.cap * kEmbDim * 2);
+  p->in_slab<void>("mbx_rows", sl.mbx_rows, static_cast<size_t>(cfg->world) * sh.cap * 4);
+  p->in_slab<void>("mbx_dl", sl.mbx_dl, static_cast<size_t>(cfg->world) * sh.cap * 4);
+  p->in_slab<void>("mbx_count", sl.mbx_count, kMaxWorld * 4);
+
+  const size_t ne = static_cast<size_t>(sh.rows_local) * kEmbDim;
+  const bool has1 = cfg->optimizer != WD_SGD, has2 = cfg->optimizer == WD_ADAM;
+  bool ok = true;
+  ok &= (p->emb_master = p->alloc<float>("emb_master", ne)) != nullptr;
+  if (has1) ok &= (p->emb_s1 = p->alloc<float>("emb_slot1", ne)) != nullptr;
+  if (has2) ok &= (p->emb_s2 = p->alloc<float>("emb_slot2", ne)) != nullptr;
+  if (has1) ok &= (p->wide_s1 = p->alloc<float>("wide_slot1", sh.rows_local)) != nullptr;
+  if (has2) ok &= (p->wide_s2 = p->alloc<float>("wide_slot2", sh.rows_local)) != nullptr;
+  if (cfg->sync) {
+    ok &= (p->G = p->alloc<float>("emb_grad_accum", ne)) != nullptr;
+    ok &= (p->wide_G = p->alloc<float>("wide_grad_accum", sh.rows_local)) != nullptr;
+    p->bitmap_words = (sh.rows_local + 31) / 32;
+    ok &= (p->bitmap = p->alloc<unsigned int>("touched_bitmap", p->bitmap_words)) != nullptr;
+  }
+  ok &= (p->dense_master = p->alloc<float>("dense_master", chunk)) != nullptr;
+  if (has1) ok &= (p->dense_s1 = p->alloc<float>("dense_slot1", chunk)) != nullptr;
+  if (has2) ok &= (p->dense_s2 = p->alloc<float>("dense_slot2", chunk)) != nullptr;
+  const size_t B = sh.B;
+  ok &= (p->a_buf = p->alloc<__nv_bfloat16>("a_buf", B * sh.K0)) != nullptr;
+  ok &= (p->dense_x = p->alloc<__nv_bfloat16>("dense_x", B * sh.dense_pad)) != nullptr;
+  ok &= (p->H1 = p->alloc<__nv_bfloat16>("h1", B * sh.h1)) != nullptr;
+  ok &= (p->H2 = p->alloc<__nv_bfloat16>("h2", B * sh.h2)) != nullptr;
+  ok &= (p->H3 = p->alloc<__nv_bfloat16>("h3", B * sh.h3)) != nullptr;
+  ok &= (p->dZ1 = p->alloc<__nv_bfloat16>("dz1", B * sh.h1)) != nullptr;
+  ok &= (p->dZ2 = p->alloc<__nv_bfloat16>("dz2", B * sh.h2)) != nullptr;
+  ok &= (p->dZ3 = p->alloc<__nv_bfloat16>("dz3", B * sh.h3)) != nullptr;
+  p->ldm1 = mask_ld(sh.h1); p->ldm2 = mask_ld(sh.h2); p->ldm3 = mask_ld(sh.h3);
+  ok &= (p->m1 = p->alloc<uint32_t>("mask1", B * p->ldm1)) != nullptr;
+  ok &= (p->m2 = p->alloc<uint32_t>("mask2", B * p->ldm2)) != nullptr;
+  ok &= (p->m3 = p->alloc<uint32_t>("mask3", B * p->ldm3)) != nullptr;
+  ok &= (p->row_src = p->alloc<unsigned long long>("row_src", sh.cap)) != nullptr;
+  ok &= (p->wide_src = p->alloc<unsigned long long>("wide_src", sh.cap)) != nullptr;
+  ok &= (p->row_dst = p->alloc<unsigned long long>("row_dst", sh.cap)) != nullptr;
+  ok &= (p->dl_dst = p->alloc<unsigned long long>("dl_dst", sh.cap)) != nullptr;
+  ok &= (p->dlogit = p->alloc<float>("dlogit", B)) != nullptr;
+  ok &= (p->prob = p->alloc<float>("prob", B)) != nullptr;
+  const int m_tiles = (sh.B + BM - 1) / BM;
+  p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles) * 4;
+  ok &= (p->zero_region = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles)) != nullptr;
+  if (!ok) {
+    dtf_wd_destroy(p);
+    return nullptr;
+  }
+  p->cnt = p->zero_region;
+  p->chunk_counter = p->zero_region + kMaxWorld;
+  p->loss_acc = reinterpret_cast<float*>(p->zero_region + kMaxWorld + 4);
+  p->tile_flags = p->zero_region + kMaxWorld + 8;
+  return p;
+}
+
+void dtf_wd_destroy(dtf_wd_plan* p) {
+  if (!p) return;
+  cudaDeviceSynchronize();
+  for (void* m : p->opened) cudaIpcCloseMemHandle(m);
+  for (void* q : p->owned) cudaFree(q);
+  if (p->slab && p->owns_slab) cudaFree(p->slab);
+  (void)cudaGetLastError();
+  delete p;
+}
+
+int dtf_wd_buffer(dtf_wd_plan* p, const char* name, void** ptr, size_t* bytes) {
+  auto it = p->bufs.find(name);
+  if (it == p->bufs.end()) {
+    set_error("wd plan: no buffer named '%s'", name);
+    return -2;
+  }
+  *ptr = it->second.ptr;
+  *bytes = it->second.bytes;
+  return 0;
+}
+
+int dtf_wd_info(dtf_wd_plan* p, dtf_wd_info_t* out) {
+  memset(out, 0, sizeof(*out));
+  out->K0 = p->sh.K0;
+  out->rows_local = p->sh.rows_local;
+  out->P = p->dl.P;
+  out->P_pad = p->P_pad;
+  out->dense_lo = p->dense_lo;
+  out->dense_hi = p->dense_hi;
+  out->off_w1 = p->dl.w1; out->off_w2 = p->dl.w2; out->off_w3 = p->dl.w3;
+  out->off_b1 = p->dl.b1; out->off_b2 = p->dl.b2; out->off_b3 = p->dl.b3;
+  out->off_w4 = p->dl.w4; out->off_b4 = p->dl.b4; out->off_wide_b = p->dl.wide_b;
+  out->small_begin = p->dl.small_begin;
+  out->slab_bytes = static_cast<long long>(p->sl.total);
+  out->step = p->step;
+  return 0;
+}
+
+int dtf_wd_slab_handle(dtf_wd_plan* p, void* handle_out) { return dtf_symm_get_handle(p->slab, handle_out); }
+void* dtf_wd_slab_ptr(dtf_wd_plan* p) { return p->slab; }
+
+// handles: world * dtf_symm_handle_size() bytes (own entry ignored)
+int dtf_wd_attach_ipc(dtf_wd_plan* p, const void* handles) {
+  const int hs = dtf_symm_handle_size();
+  for (int r = 0; r < p->cfg.world; ++r) {
+    if (r == p->cfg.rank) continue;
+    void* m = nullptr;
+    if (dtf_symm_open_handle(static_cast<const uint8_t*>(handles) + static_cast<size_t>(r) * hs, &m) != 0) return -1;
+    p->opened.push_back(m);
+    p->pt.slab[r] = static_cast<uint8_t*>(m);
+  }
+  return 0;
+}
+
+// same-process peers: raw slab pointers of the other plans (tests, single-process multi-GPU)
+int dtf_wd_attach_ptrs(dtf_wd_plan* p, void* const* slabs) {
+  for (int r = 0; r < p->cfg.world; ++r)
+    if (r != p->cfg.rank) p->pt.slab[r] = static_cast<uint8_t*>(slabs[r]);
+  return 0;
+}
+
+int dtf_wd_init_params(dtf_wd_plan* p, unsigned long long seed, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  const float slot1_init = p->cfg.optimizer == WD_ADAGRAD ? 0.1f : 0.f;
+  wd_init_embedding_kernel<<<num_sms() * 8, 256, 0, st>>>(
+      p->emb_master, reinterpret_cast<__nv_bfloat16*>(p->slab + p->sl.emb_bf16), p->emb_s1, p->emb_s2,
+      reinterpret_cast<float*>(p->slab + p->sl.wide), p->wide_s1, p->wide_s2, p->sh.rows_local, p->cfg.world,
+      p->cfg.rank, seed, p->cfg.emb_init_scale, slot1_init);
+  wd_init_dense_kernel<<<num_sms() * 4, 256, 0, st>>>(p->dense_master, p->dense_s1, p->dense_s2, p->dense_lo,
+                                                      p->dense_hi, p->dl, p->sh, seed, slot1_init);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch(2);
+  return dtf_wd_broadcast_dense(p, stream_);
+}
+
+// push this rank's dense master range into every peer's working copy (needs peers attached)
+int dtf_wd_broadcast_dense(dtf_wd_plan* p, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  wd_dense_broadcast_kernel<<<num_sms() * 4, 256, 0, st>>>(p->dense_master, p->dense_lo, p->dense_hi, p->pt, p->sl,
+                                                           p->dl.small_begin);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// refresh the bf16 working copy of the embedding shard from the fp32 master (after a restore)
+__global__ void wd_refresh_emb_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ work, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    work[i] = __float2bfloat16(master[i]);
+}
+int dtf_wd_refresh_embedding(dtf_wd_plan* p, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  wd_refresh_emb_kernel<<<num_sms() * 8, 256, 0, st>>>(
+      p->emb_master, reinterpret_cast<__nv_bfloat16*>(p->slab + p->sl.emb_bf16), p->sh.rows_local * kEmbDim);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------ step
+static GemmArgs base_args(cudaStream_t st) {
+  GemmArgs a{};
+  a.stream = st;
+  a.splits = 1;
+  return a;
+}
+
+static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaStream_t st, bool train) {
+  const WdShapes& sh = p->sh;
+  const DenseLayout& dl = p->dl;
+  const int n = static_cast<int>(sh.cap);
+  DTF_CUDA_OK(cudaMemsetAsync(p->zero_region, 0, p->zero_bytes, st));
+  wd_route_kernel<<<(n + 255) / 256, 256, 0, st>>>(ids, n, sh.V, p->pt, p->sl, sh.cap, p->cnt, p->row_src, p->wide_src,
+                                                   p->row_dst, p->dl_dst);
+  wd_dense_pad_kernel<<<(sh.B * sh.dense_pad + 255) / 256, 256, 0, st>>>(dense_raw, p->dense_x, sh.B, sh.dense_in,
+                                                                         sh.dense_pad);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch(2);
+  const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
+  const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
+  // layer 1: embedding pull fused with the GEMM
+  GemmArgs a = base_args(st);
+  a.A = p->a_buf; a.lda = sh.K0; a.B = W + dl.w1; a.ldb = sh.K0; a.D = p->H1; a.ldd = sh.h1;
+  a.M = sh.B; a.N = sh.h1; a.K = sh.K0; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b1 - dl.small_begin);
+  a.mask_out = train ? p->m1 : nullptr; a.ldmask = p->ldm1;
+  a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
+  a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
+  if (launch_gemm_gather(a) != 0) return -1;
+  // layers 2, 3
+  a = base_args(st);
+  a.A = p->H1; a.lda = sh.h1; a.B = W + dl.w2; a.ldb = sh.h1; a.D = p->H2; a.ldd = sh.h2;
+  a.M = sh.B; a.N = sh.h2; a.K = sh.h1; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b2 - dl.small_begin);
+  a.mask_out = train ? p->m2 : nullptr; a.ldmask = p->ldm2;
+  if (launch_gemm_kk(a) != 0) return -1;
+  a = base_args(st);
+  a.A = p->H2; a.lda = sh.h2; a.B = W + dl.w3; a.ldb = sh.h2; a.D = p->H3; a.ldd = sh.h3;
+  a.M = sh.B; a.N = sh.h3; a.K = sh.h2; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b3 - dl.small_begin);
+  a.mask_out = train ? p->m3 : nullptr; a.ldmask = p->ldm3;
+  if (launch_gemm_kk(a) != 0) return -1;
+  return 0;
+}
+
+static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, bool train) {
+  const WdShapes& sh = p->sh;
+  const DenseLayout& dl = p->dl;
+  const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
+  float* g_small = reinterpret_cast<float*>(p->slab + p->sl.dense_grad) + dl.small_begin;
+  const int off_w4 = static_cast<int>(dl.w4 - dl.small_begin), off_b4 = static_cast<int>(dl.b4 - dl.small_begin),
+            off_wb = static_cast<int>(dl.wide_b - dl.small_begin);
+  const float inv_batch = 1.0f / (static_cast<float>(sh.B) * (p->cfg.sync ? p->cfg.world : 1));
+  int grid = num_sms() * 2;
+  if (grid > (sh.B + 7) / 8) grid = (sh.B + 7) / 8;
+  if (train) {
+    const size_t smem = 8 * (sh.h3 + 2) * sizeof(float);
+    wd_loss_kernel<true><<<grid, 256, smem, st>>>(p->H3, p->m3, p->ldm3, small, off_w4, off_b4, off_wb, p->wide_src,
+                                                  p->dl_dst, labels, sh.B, sh.F, sh.h3, inv_batch, p->dlogit, p->dZ3,
+                                                  g_small, p->loss_acc, nullptr);
+  } else {
+    wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_src, nullptr,
+                                                nullptr, sh.B, sh.F, sh.h3, 0.f, nullptr, nullptr, nullptr, nullptr,
+                                                p->prob);
+  }
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+static int wgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n_out, const __nv_bfloat16* x, int k_in, long long off,
+                 cudaStream_t st) {
+  // dW[n_out, k_in] += dy^T x, reduction over the batch; partial tiles are added by TMA reduce
+  GemmArgs a = base_args(st);
+  a.A = dy; a.lda = n_out; a.a_mn = true; a.B = x; a.ldb = k_in; a.b_mn = true;
+  a.D = reinterpret_cast<float*>(p->slab + p->sl.dense_grad) + off; a.ldd = k_in;
+  a.M = n_out; a.N = k_in; a.K = p->sh.B; a.epi = EPI_F32_ATOMIC;
+  const int tiles = ((n_out + BM - 1) / BM) * ((k_in + 255) / 256);
+  int splits = num_sms() / (tiles > 0 ? tiles : 1);
+  const int kb = (p->sh.B + BK - 1) / BK;
+  if (splits > kb) splits = kb;
+  if (splits < 1) splits = 1;
+  a.splits = splits;
+  a.bn = 256;
+  return launch_gemm_mnmn(a);
+}
+
+static int dgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n, const __nv_bfloat16* w, int k, const uint32_t* mask,
+                 int ldmask, __nv_bfloat16* out, cudaStream_t st) {
+  GemmArgs a = base_args(st);
+  a.A = dy; a.lda = n; a.B = w; a.ldb = k; a.b_mn = true; a.D = out; a.ldd = k;
+  a.M = p->sh.B; a.N = k; a.K = n; a.epi = EPI_DRELU_BF16; a.mask_in = mask; a.ldmask = ldmask;
+  return launch_gemm_kmn(a);
+}
+
+static int colsum(const __nv_bfloat16* x, int M, int N, float* out, cudaStream_t st) {
+  const int rpb = 256;
+  dim3 grid((N + 63) / 64, (M + rpb - 1) / rpb);
+  wd_colsum_kernel<<<grid, 256, 0, st>>>(x, M, N, N, rpb, out);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+template <int OPT>
+static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
+  const SlabLayout& sl = p->sl;
+  MailboxView mv{};
+  mv.payload = reinterpret_cast<const __nv_bfloat16*>(p->slab + sl.mbx_payload);
+  mv.rows = reinterpret_cast<const int*>(p->slab + sl.mbx_rows);
+  mv.dl = reinterpret_cast<const float*>(p->slab + sl.mbx_dl);
+  mv.count = reinterpret_cast<const unsigned int*>(p->slab + sl.mbx_count);
+  mv.cap = p->sh.cap;
+  mv.world = p->cfg.world;
+  const OptConst oc = opt_const(p, p->step + 1);
+  __nv_bfloat16* work = reinterpret_cast<__nv_bfloat16*>(p->slab + sl.emb_bf16);
+  float* wide = reinterpret_cast<float*>(p->slab + sl.wide);
+  const int grid = num_sms() * 8;
+  if (p->cfg.sync) {
+    wd_sparse_accum_kernel<<<grid, 256, 0, st>>>(mv, p->G, p->wide_G, p->bitmap);
+    wd_sparse_apply_rows_kernel<OPT><<<grid, 256, 0, st>>>(p->bitmap, p->bitmap_words, p->G, p->wide_G, p->emb_master,
+                                                           p->emb_s1, p->emb_s2, work, wide, p->wide_s1, p->wide_s2, oc);
+    count_launch(2);
+  } else {
+    wd_sparse_apply_entries_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
+                                                              p->wide_s1, p->wide_s2, oc);
+    count_launch();
+  }
+  if (p->cfg.sync) {
+    wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, 0, p->cfg.world,
+                                                              p->dense_master, p->dense_s1, p->dense_s2, oc,
+                                                              p->dl.small_begin);
+    count_launch();
+  } else {
+    // Hogwild on the dense shard: each replica's gradient is applied on its own, in rank order
+    for (int r = 0; r < p->cfg.world; ++r) {
+      wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, r, r + 1,
+                                                                p->dense_master, p->dense_s1, p->dense_s2, oc,
+                                                                p->dl.small_begin);
+      count_launch();
+    }
+  }
+  DTF_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" {
+
+// forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
+// [B*dense_in], labels f32 [B]
+int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  const WdShapes& sh = p->sh;
+  const DenseLayout& dl = p->dl;
+  DTF_CUDA_OK(cudaMemsetAsync(p->slab + p->sl.dense_grad, 0, static_cast<size_t>(p->P_pad) * 4, st));
+  if (forward(p, ids, dense_raw, st, true) != 0) return -1;
+  if (launch_loss(p, labels, st, true) != 0) return -1;
+  const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
+  float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
+  if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
+  if (dgrad(p, p->dZ3, sh.h3, W + dl.w3, sh.h2, p->m2, p->ldm2, p->dZ2, st) != 0) return -1;
+  if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
+  if (dgrad(p, p->dZ2, sh.h2, W + dl.w2, sh.h1, p->m1, p->ldm1, p->dZ1, st) != 0) return -1;
+  if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st) != 0) return -1;
+  if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
+  if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
+  if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
+  // fused push: dA = dZ1 W1[:, :F*128]; every 128-wide row goes to its owner's mailbox
+  GemmArgs a = base_args(st);
+  a.A = p->dZ1; a.lda = sh.h1; a.B = W + dl.w1; a.ldb = sh.K0; a.b_mn = true;
+  a.M = sh.B; a.N = sh.F * kEmbDim; a.K = sh.h1; a.epi = EPI_PUSH_ROWS; a.row_dst = p->row_dst; a.slots = sh.F;
+  a.bn = 256;
+  if (launch_gemm_kmn(a) != 0) return -1;
+  return 0;
+}
+
+// cross-rank barrier on the device (no-op publish for a single rank)
+int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  if (p->cfg.world == 1 || p->cfg.no_device_barrier) {
+    if (publish_counts) {
+      wd_publish_local_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->cnt);
+      count_launch();
+    }
+  } else {
+    p->epoch += 1;
+    wd_barrier_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->epoch, publish_counts ? p->cnt : nullptr);
+    count_launch();
+  }
+  DTF_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// parameter-server side: apply what the mailboxes and gradient buffers hold
+int dtf_wd_step_apply(dtf_wd_plan* p, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  int rc;
+  switch (p->cfg.optimizer) {
+    case WD_SGD: rc = apply_t<WD_SGD>(p, st); break;
+    case WD_ADAGRAD: rc = apply_t<WD_ADAGRAD>(p, st); break;
+    default: rc = apply_t<WD_ADAM>(p, st); break;
+  }
+  if (rc == 0) p->step += 1;
+  return rc;
+}
+
+int dtf_wd_step(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, void* stream_) {
+  if (dtf_wd_step_compute(p, ids, dense_raw, labels, stream_) != 0) return -1;
+  if (dtf_wd_barrier(p, 1, stream_) != 0) return -1;   // every push and gradient has landed
+  if (dtf_wd_step_apply(p, stream_) != 0) return -1;
+  if (p->cfg.world > 1 && dtf_wd_barrier(p, 0, stream_) != 0) return -1;  // updated shards visible to all
+  return 0;
+}
+
+// serving / evaluation forward: probabilities for B examples into the plan's "prob" buffer
+int dtf_wd_predict(dtf_wd_plan* p, const int* ids, const float* dense_raw, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  if (forward(p, ids, dense_raw, st, false) != 0) return -1;
+  return launch_loss(p, nullptr, st, false);
+}
+
+// sum of per-example losses of the last step (device -> host, synchronises the stream)
+int dtf_wd_read_loss(dtf_wd_plan* p, float* loss_sum, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_CUDA_OK(cudaMemcpyAsync(loss_sum, p->loss_acc, sizeof(float), cudaMemcpyDeviceToHost, st));
+  DTF_CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+void* dtf_wd_loss_ptr(dtf_wd_plan* p) { return p->loss_acc; }
+
+}  // extern "C"

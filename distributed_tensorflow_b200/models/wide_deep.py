@@ -1,0 +1,357 @@
+"""Wide-and-deep on the B200-native parameter server (north-star configs 3 and 4).
+
+Model::
+
+    deep : concat(emb[id_1] .. emb[id_F], dense[0:dense_in] zero-padded to dense_pad)
+           -> Linear(K0, h1) ReLU -> Linear(h1, h2) ReLU -> Linear(h2, h3) ReLU -> Linear(h3, 1)
+    wide : sum_f wide_w[id_f] + wide_b
+    loss : mean sigmoid cross-entropy of (deep + wide) against the label
+
+Every rank is worker and parameter-server shard at once: embedding / wide row ``r`` lives in the HBM
+of rank ``r % world``, the flat dense parameter vector is range-partitioned.  The training step is
+executed by the C++ plan (``csrc/kernels/wd_plan.cu``): one ctypes call launches route, fused pull
+(peer-HBM gather + tcgen05 GEMM-1), the MLP, loss, backward, fused push (dgrad GEMM scattering rows
+into the owners' mailboxes) and the ps-side optimizer applies.  This is the scale-up of the
+reference's ps/worker training loop (/root/reference/trainer/task.py:123-143, 232-246) -- async
+(Hogwild) like the reference, plus the sync-replica mode of the north star.
+
+:class:`TorchReference` restates the same step in plain PyTorch fp32 and is the numerics oracle.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, asdict
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from ..ops import _lib
+
+OPT_IDS = {"sgd": 0, "adagrad": 2, "adam": 3}
+
+
+@dataclass
+class WideDeepConfig:
+    emb_rows: int = 10_000_000
+    emb_dim: int = 128
+    slots: int = 26
+    dense_in: int = 13
+    dense_pad: int = 64
+    h1: int = 1024
+    h2: int = 512
+    h3: int = 256
+    batch: int = 8192            # per rank
+    optimizer: str = "adagrad"
+    lr: float = 0.05
+    sync: bool = False           # False = async / Hogwild (the reference's semantics)
+    emb_init_scale: float = 0.05
+    seed: int = 1234
+
+    @property
+    def k0(self) -> int:
+        return self.slots * self.emb_dim + self.dense_pad
+
+
+class _CConfig(C.Structure):
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("batch", C.c_int), ("slots", C.c_int), ("emb_dim", C.c_int),
+                ("dense_in", C.c_int), ("dense_pad", C.c_int), ("h1", C.c_int), ("h2", C.c_int), ("h3", C.c_int),
+                ("emb_rows", C.c_longlong), ("optimizer", C.c_int), ("sync", C.c_int), ("no_device_barrier", C.c_int),
+                ("lr", C.c_float), ("emb_init_scale", C.c_float)]
+
+
+class _CInfo(C.Structure):
+    _fields_ = [("K0", C.c_int)] + [(n, C.c_longlong) for n in (
+        "rows_local", "P", "P_pad", "dense_lo", "dense_hi", "off_w1", "off_w2", "off_w3", "off_b1", "off_b2", "off_b3",
+        "off_w4", "off_b4", "off_wide_b", "small_begin", "slab_bytes", "step")]
+
+
+class _DevArray:
+    """Zero-copy view of a raw device pointer for ``torch.as_tensor``."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+_TYPESTR = {torch.float32: ("<f4", 4), torch.int32: ("<i4", 4), torch.uint8: ("|u1", 1), torch.int16: ("<i2", 2),
+            torch.int64: ("<i8", 8)}
+
+
+def _bind(L):
+    if getattr(L, "_wd_bound", False):
+        return
+    vp, i = C.c_void_p, C.c_int
+    L.dtf_wd_create.restype = vp
+    L.dtf_wd_create.argtypes = [C.POINTER(_CConfig)]
+    L.dtf_wd_destroy.restype = None
+    L.dtf_wd_destroy.argtypes = [vp]
+    L.dtf_wd_info.argtypes = [vp, C.POINTER(_CInfo)]
+    L.dtf_wd_buffer.argtypes = [vp, C.c_char_p, C.POINTER(vp), C.POINTER(C.c_size_t)]
+    L.dtf_wd_slab_handle.argtypes = [vp, vp]
+    L.dtf_wd_slab_ptr.restype = vp
+    L.dtf_wd_slab_ptr.argtypes = [vp]
+    L.dtf_wd_attach_ipc.argtypes = [vp, vp]
+    L.dtf_wd_attach_ptrs.argtypes = [vp, C.POINTER(vp)]
+    L.dtf_wd_init_params.argtypes = [vp, C.c_ulonglong, vp]
+    L.dtf_wd_broadcast_dense.argtypes = [vp, vp]
+    L.dtf_wd_refresh_embedding.argtypes = [vp, vp]
+    for fn in (L.dtf_wd_step_compute, L.dtf_wd_step):
+        fn.argtypes = [vp, vp, vp, vp, vp]
+    L.dtf_wd_barrier.argtypes = [vp, i, vp]
+    L.dtf_wd_step_apply.argtypes = [vp, vp]
+    L.dtf_wd_predict.argtypes = [vp, vp, vp, vp]
+    L.dtf_wd_read_loss.argtypes = [vp, C.POINTER(C.c_float), vp]
+    L.dtf_wd_loss_ptr.restype = vp
+    L.dtf_wd_loss_ptr.argtypes = [vp]
+    L.dtf_symm_handle_size.restype = i
+    L._wd_bound = True
+
+
+class WideDeepTrainer:
+    """One rank of the wide-and-deep job (worker + ps shard)."""
+
+    name = "wide_deep"
+
+    def __init__(self, cfg: WideDeepConfig, rank: int = 0, world: int = 1, device: Optional[torch.device] = None,
+                 no_device_barrier: bool = False):
+        if not torch.cuda.is_available():
+            raise RuntimeError("wide_deep needs a CUDA device (B200); the toy linear model is the CPU path")
+        self.cfg, self.rank, self.world = cfg, rank, world
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self._L = _lib.lib()
+        _bind(self._L)
+        cc = _CConfig(world=world, rank=rank, batch=cfg.batch, slots=cfg.slots, emb_dim=cfg.emb_dim,
+                      dense_in=cfg.dense_in, dense_pad=cfg.dense_pad, h1=cfg.h1, h2=cfg.h2, h3=cfg.h3,
+                      emb_rows=cfg.emb_rows, optimizer=OPT_IDS[cfg.optimizer], sync=int(cfg.sync),
+                      no_device_barrier=int(no_device_barrier), lr=cfg.lr, emb_init_scale=cfg.emb_init_scale)
+        with torch.cuda.device(self.device):
+            self._h = self._L.dtf_wd_create(C.byref(cc))
+        if not self._h:
+            raise _lib.KernelError("dtf_wd_create: " + self._L.dtf_last_error().decode())
+        self.info = _CInfo()
+        self._L.dtf_wd_info(self._h, C.byref(self.info))
+        self._attached = world == 1
+        self._views: Dict[str, torch.Tensor] = {}
+        self.loss_view = self.buffer("step_scratch", torch.float32)[20:21]   # loss_acc lives after cnt + counter
+
+    # ------------------------------------------------------------------ set-up
+    def slab_handle(self) -> bytes:
+        n = self._L.dtf_symm_handle_size()
+        buf = C.create_string_buffer(n)
+        _lib.check(self._L.dtf_wd_slab_handle(self._h, buf), "dtf_wd_slab_handle")
+        return buf.raw
+
+    def slab_ptr(self) -> int:
+        return int(self._L.dtf_wd_slab_ptr(self._h))
+
+    def attach_ipc(self, handles: List[bytes]) -> None:
+        blob = b"".join(handles)
+        with torch.cuda.device(self.device):
+            _lib.check(self._L.dtf_wd_attach_ipc(self._h, blob), "dtf_wd_attach_ipc")
+        self._attached = True
+
+    def attach_local(self, peers: List["WideDeepTrainer"]) -> None:
+        """Peers living in this process (several ranks emulated on one device, or one process
+        driving several GPUs)."""
+        arr = (C.c_void_p * self.world)(*[p.slab_ptr() for p in peers])
+        _lib.check(self._L.dtf_wd_attach_ptrs(self._h, arr), "dtf_wd_attach_ptrs")
+        self._attached = True
+
+    def init_params(self, seed: Optional[int] = None) -> None:
+        assert self._attached, "attach peers before initialising (owners broadcast their dense shard)"
+        with torch.cuda.device(self.device):
+            _lib.check(self._L.dtf_wd_init_params(self._h, seed if seed is not None else self.cfg.seed, self._stream()),
+                       "dtf_wd_init_params")
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ------------------------------------------------------------------ buffers
+    def buffer(self, name: str, dtype=torch.float32, shape=None) -> torch.Tensor:
+        """Zero-copy torch view of a named plan buffer (bf16 buffers: pass torch.bfloat16)."""
+        key = "%s/%s/%s" % (name, dtype, shape)
+        if key in self._views:
+            return self._views[key]
+        ptr, nbytes = C.c_void_p(), C.c_size_t()
+        _lib.check(self._L.dtf_wd_buffer(self._h, name.encode(), C.byref(ptr), C.byref(nbytes)), "dtf_wd_buffer")
+        base_dtype = torch.int16 if dtype == torch.bfloat16 else dtype
+        typestr, isz = _TYPESTR[base_dtype]
+        n = nbytes.value // isz
+        with torch.cuda.device(self.device):
+            t = torch.as_tensor(_DevArray(ptr.value, (n,), typestr), device=self.device)
+        if dtype == torch.bfloat16:
+            t = t.view(torch.bfloat16)
+        if shape is not None:
+            t = t[: int(np.prod(shape))].view(*shape)
+        self._views[key] = t
+        return t
+
+    def dense_views(self) -> Dict[str, torch.Tensor]:
+        """fp32 views into this rank's *gradient* buffer and (world == 1 only) master weights, by layer."""
+        c, inf = self.cfg, self.info
+        out = {}
+        for src, prefix in (("dense_grad", "grad_"), ("dense_master", "")):
+            if src == "dense_master" and self.world != 1:
+                continue
+            flat = self.buffer(src, torch.float32)
+            out[prefix + "w1"] = flat[inf.off_w1: inf.off_w1 + c.h1 * inf.K0].view(c.h1, inf.K0)
+            out[prefix + "w2"] = flat[inf.off_w2: inf.off_w2 + c.h2 * c.h1].view(c.h2, c.h1)
+            out[prefix + "w3"] = flat[inf.off_w3: inf.off_w3 + c.h3 * c.h2].view(c.h3, c.h2)
+            out[prefix + "b1"] = flat[inf.off_b1: inf.off_b1 + c.h1]
+            out[prefix + "b2"] = flat[inf.off_b2: inf.off_b2 + c.h2]
+            out[prefix + "b3"] = flat[inf.off_b3: inf.off_b3 + c.h3]
+            out[prefix + "w4"] = flat[inf.off_w4: inf.off_w4 + c.h3]
+            out[prefix + "b4"] = flat[inf.off_b4: inf.off_b4 + 1]
+            out[prefix + "wide_b"] = flat[inf.off_wide_b: inf.off_wide_b + 1]
+        return out
+
+    # ------------------------------------------------------------------ stepping
+    def _ptrs(self, ids, dense, labels=None):
+        assert ids.dtype == torch.int32 and ids.is_cuda and ids.is_contiguous() and ids.numel() == self.cfg.batch * self.cfg.slots
+        assert dense.dtype == torch.float32 and dense.is_contiguous() and dense.numel() == self.cfg.batch * self.cfg.dense_in
+        if labels is not None:
+            assert labels.dtype == torch.float32 and labels.numel() == self.cfg.batch
+        return C.c_void_p(ids.data_ptr()), C.c_void_p(dense.data_ptr()), C.c_void_p(labels.data_ptr() if labels is not None else 0)
+
+    def step(self, ids: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor) -> None:
+        """One full training step on device-resident inputs (asynchronous)."""
+        a, b, c = self._ptrs(ids, dense, labels)
+        _lib.check(self._L.dtf_wd_step(self._h, a, b, c, self._stream()), "dtf_wd_step")
+
+    def step_compute(self, ids, dense, labels) -> None:
+        a, b, c = self._ptrs(ids, dense, labels)
+        _lib.check(self._L.dtf_wd_step_compute(self._h, a, b, c, self._stream()), "dtf_wd_step_compute")
+
+    def barrier(self, publish_counts: bool) -> None:
+        _lib.check(self._L.dtf_wd_barrier(self._h, int(publish_counts), self._stream()), "dtf_wd_barrier")
+
+    def step_apply(self) -> None:
+        _lib.check(self._L.dtf_wd_step_apply(self._h, self._stream()), "dtf_wd_step_apply")
+
+    def predict(self, ids: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
+        a, b, _ = self._ptrs(ids, dense)
+        _lib.check(self._L.dtf_wd_predict(self._h, a, b, self._stream()), "dtf_wd_predict")
+        return self.buffer("prob", torch.float32)
+
+    def last_loss_sum(self) -> torch.Tensor:
+        """Device scalar: sum over the micro-batch of the per-example loss of the last step."""
+        return self.loss_view
+
+    def global_step(self) -> int:
+        self._L.dtf_wd_info(self._h, C.byref(self.info))
+        return int(self.info.step)
+
+    def close(self) -> None:
+        if self._h:
+            self._views.clear()
+            self._L.dtf_wd_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class TorchReference:
+    """The same step in plain PyTorch (fp32 math on bf16-rounded operands) for ``world`` replicas that
+    share one parameter set -- the oracle for the CUDA path."""
+
+    def __init__(self, cfg: WideDeepConfig, emb: torch.Tensor, wide: torch.Tensor, dense: Dict[str, torch.Tensor]):
+        self.cfg = cfg
+        self.emb, self.wide = emb.clone().float(), wide.clone().float()
+        self.p = {k: v.clone().float() for k, v in dense.items()}
+        init = 0.1 if cfg.optimizer == "adagrad" else 0.0
+        self.s1 = {k: torch.full_like(v, init) for k, v in self._all().items()}
+        self.s2 = {k: torch.zeros_like(v) for k, v in self._all().items()}
+        self.t = 0
+
+    def _all(self):
+        d = dict(self.p)
+        d["emb"], d["wide"] = self.emb, self.wide
+        return d
+
+    @staticmethod
+    def _bf(x):
+        return x.to(torch.bfloat16).float()
+
+    def forward(self, ids, dense):
+        c = self.cfg
+        B = ids.shape[0]
+        e = self._bf(self.emb)[ids.long()].reshape(B, c.slots * c.emb_dim)
+        x = torch.zeros(B, c.dense_pad, device=ids.device)
+        x[:, :c.dense_in] = dense
+        a = torch.cat([e, self._bf(x)], dim=1)
+        p = self.p
+        z1 = a @ self._bf(p["w1"]).t() + p["b1"]
+        h1 = self._bf(torch.relu(z1))
+        z2 = h1 @ self._bf(p["w2"]).t() + p["b2"]
+        h2 = self._bf(torch.relu(z2))
+        z3 = h2 @ self._bf(p["w3"]).t() + p["b3"]
+        h3 = self._bf(torch.relu(z3))
+        logit = h3 @ p["w4"] + p["b4"] + self.wide[ids.long()].sum(1) + p["wide_b"]
+        return a, h1, h2, h3, logit
+
+    def grads(self, ids, dense, labels, denom):
+        """Gradients of sum(loss)/denom; returns (loss_sum, dense grads, emb row grads [B,F,128], dlogit)."""
+        c = self.cfg
+        a, h1, h2, h3, logit = self.forward(ids, dense)
+        loss = torch.nn.functional.binary_cross_entropy_with_logits(logit, labels, reduction="sum")
+        dl = (torch.sigmoid(logit) - labels) / denom
+        p = self.p
+        g = {"w4": h3.t() @ dl, "b4": dl.sum().view(1), "wide_b": dl.sum().view(1)}
+        dz3 = self._bf((dl[:, None] * p["w4"][None, :]) * (h3 > 0))
+        g["w3"], g["b3"] = dz3.t() @ h2, dz3.sum(0)
+        dz2 = self._bf((dz3 @ self._bf(p["w3"])) * (h2 > 0))
+        g["w2"], g["b2"] = dz2.t() @ h1, dz2.sum(0)
+        dz1 = self._bf((dz2 @ self._bf(p["w2"])) * (h1 > 0))
+        g["w1"], g["b1"] = dz1.t() @ a, dz1.sum(0)
+        da = self._bf(dz1 @ self._bf(p["w1"])[:, : c.slots * c.emb_dim]).view(-1, c.slots, c.emb_dim)
+        return loss, g, da, dl
+
+    def _apply(self, name, w, g, rows=None):
+        c = self.cfg
+        s1, s2 = self.s1[name], self.s2[name]
+        if rows is not None:
+            w_, s1_, s2_ = w[rows], s1[rows], s2[rows]
+        else:
+            w_, s1_, s2_ = w, s1, s2
+        if c.optimizer == "sgd":
+            w_ = w_ - c.lr * g
+        elif c.optimizer == "adagrad":
+            s1_ = s1_ + g * g
+            w_ = w_ - c.lr * g / s1_.sqrt()
+        else:
+            lr_t = c.lr * (1 - 0.999 ** self.t) ** 0.5 / (1 - 0.9 ** self.t)
+            s1_ = 0.9 * s1_ + 0.1 * g
+            s2_ = 0.999 * s2_ + 0.001 * g * g
+            w_ = w_ - lr_t * s1_ / (s2_.sqrt() + 1e-8)
+        if rows is not None:
+            w[rows], s1[rows], s2[rows] = w_, s1_, s2_
+        else:
+            w.copy_(w_), s1.copy_(s1_), s2.copy_(s2_)
+
+    def sync_step(self, batches):
+        """Sync-replica: gradients of all replicas' micro-batches are summed, one apply."""
+        c = self.cfg
+        self.t += 1
+        denom = float(sum(b[0].shape[0] for b in batches))
+        total = 0.0
+        gsum, rows_all, da_all, dl_all = None, [], [], []
+        for ids, dense, labels in batches:
+            loss, g, da, dl = self.grads(ids, dense, labels, denom)
+            total += float(loss)
+            gsum = g if gsum is None else {k: gsum[k] + g[k] for k in g}
+            rows_all.append(ids.long().reshape(-1))
+            da_all.append(da.reshape(-1, c.emb_dim))
+            dl_all.append(dl[:, None].expand(-1, c.slots).reshape(-1))
+        for k, v in gsum.items():
+            self._apply(k, self.p[k], v)
+        rows = torch.cat(rows_all)
+        uniq, inv = torch.unique(rows, return_inverse=True)
+        ge = torch.zeros(uniq.numel(), c.emb_dim, device=rows.device).index_add_(0, inv, torch.cat(da_all))
+        gw = torch.zeros(uniq.numel(), device=rows.device).index_add_(0, inv, torch.cat(dl_all))
+        self._apply("emb", self.emb, ge, rows=uniq)
+        self._apply("wide", self.wide, gw, rows=uniq)
+        return total

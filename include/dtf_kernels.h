@@ -11,11 +11,13 @@
 #ifndef DTF_KERNELS_H_
 #define DTF_KERNELS_H_
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define DTF_KERNELS_ABI_VERSION 1
+#define DTF_KERNELS_ABI_VERSION 2
 
 /* ---- bookkeeping ---------------------------------------------------------------------------- */
 const char* dtf_last_error(void);
@@ -49,6 +51,69 @@ int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long lo
                   void* D, long long ldd, int M, int N, int K, int epilogue, const float* bias,
                   const void* mask_in, void* mask_out, long long ldmask, int splits, int bn,
                   void* stream);
+
+/* ---- symmetric heap (peer-mapped HBM over NVLink / NVSwitch) --------------------------------- *
+ * Data plane that replaces the gRPC Send/Recv traffic of every sess.run in the reference
+ * (trainer/task.py:236).  Handles are opaque byte strings exchanged by the host control plane. */
+int dtf_symm_alloc(size_t bytes, void** out_ptr);             /* zero-filled */
+int dtf_symm_free(void* ptr);
+int dtf_symm_handle_size(void);
+int dtf_symm_get_handle(void* ptr, void* handle_out);
+int dtf_symm_open_handle(const void* handle, void** out_ptr); /* maps a peer's slab */
+int dtf_symm_close_handle(void* ptr);
+int dtf_symm_enable_peer(int peer_device);                    /* same-process peers */
+
+/* ---- wide-and-deep plan: the training / serving step executor -------------------------------- *
+ * Every rank is a worker and a parameter-server shard at once (embedding row r on rank
+ * r % world, dense parameters range-partitioned), the B200 mapping of the ps / worker / master
+ * roles of reference trainer/task.py:121-127.  One step = route -> fused pull (embedding gather +
+ * GEMM-1) -> MLP -> loss -> backward -> fused push (dgrad GEMM scattering rows into the owners'
+ * mailboxes) -> [barrier] -> ps-side apply (sparse scatter-add + dense reduce-scatter, each fused
+ * with SGD / Adagrad / Adam) -> [barrier].  Stands in for sess.run(train_op) (task.py:236). */
+typedef struct dtf_wd_config {
+  int world, rank;
+  int batch;          /* examples per rank per step */
+  int slots;          /* sparse ids per example (F) */
+  int emb_dim;        /* must be 128 */
+  int dense_in;       /* dense features per example */
+  int dense_pad;      /* dense block width inside the GEMM-1 operand (multiple of 64) */
+  int h1, h2, h3;     /* hidden sizes; h3 multiple of 256 */
+  long long emb_rows; /* global rows of the embedding (and wide) table */
+  int optimizer;      /* 0 sgd, 2 adagrad, 3 adam (same ids as dtf_native.h) */
+  int sync;           /* 1: sync-replica (sum all replicas, apply once); 0: async / Hogwild */
+  int no_device_barrier; /* 1: caller orders ranks itself (several ranks emulated on one GPU) */
+  float lr;
+  float emb_init_scale;
+} dtf_wd_config;
+
+typedef struct dtf_wd_info_t {
+  int K0;
+  long long rows_local, P, P_pad, dense_lo, dense_hi;
+  long long off_w1, off_w2, off_w3, off_b1, off_b2, off_b3, off_w4, off_b4, off_wide_b, small_begin;
+  long long slab_bytes, step;
+} dtf_wd_info_t;
+
+typedef struct dtf_wd_plan dtf_wd_plan;
+dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg);   /* allocates every buffer incl. the slab */
+void dtf_wd_destroy(dtf_wd_plan*);
+int dtf_wd_info(dtf_wd_plan*, dtf_wd_info_t* out);
+/* named device buffers ("emb_master", "emb_slot1", "wide", "dense_master", "dense_bf16",
+ * "dense_grad", "h1", "prob", ...) for checkpointing and tests */
+int dtf_wd_buffer(dtf_wd_plan*, const char* name, void** ptr, size_t* bytes);
+int dtf_wd_slab_handle(dtf_wd_plan*, void* handle_out);
+void* dtf_wd_slab_ptr(dtf_wd_plan*);
+int dtf_wd_attach_ipc(dtf_wd_plan*, const void* handles /* world * handle_size bytes */);
+int dtf_wd_attach_ptrs(dtf_wd_plan*, void* const* slabs /* world pointers */);
+int dtf_wd_init_params(dtf_wd_plan*, unsigned long long seed, void* stream);
+int dtf_wd_broadcast_dense(dtf_wd_plan*, void* stream);
+int dtf_wd_refresh_embedding(dtf_wd_plan*, void* stream);
+int dtf_wd_step_compute(dtf_wd_plan*, const int* ids, const float* dense, const float* labels, void* stream);
+int dtf_wd_barrier(dtf_wd_plan*, int publish_counts, void* stream);
+int dtf_wd_step_apply(dtf_wd_plan*, void* stream);
+int dtf_wd_step(dtf_wd_plan*, const int* ids, const float* dense, const float* labels, void* stream);
+int dtf_wd_predict(dtf_wd_plan*, const int* ids, const float* dense, void* stream);
+int dtf_wd_read_loss(dtf_wd_plan*, float* loss_sum, void* stream);
+void* dtf_wd_loss_ptr(dtf_wd_plan*);
 
 #ifdef __cplusplus
 }
