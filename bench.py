@@ -1,0 +1,255 @@
+#!/usr/bin/env python
+"""Headline benchmark: training examples/sec of the sharded wide-and-deep model (BASELINE.json
+configs 3/4: 10M-row embedding sharded over the ranks, 26 sparse ids + 13 dense features,
+MLP 3392-1024-512-256-1, per-rank batch 8192 => global batch 64K at 8 ranks, weak scaling).
+
+    python bench.py --gpus N --steps K --warmup W [--mode async|sync] [--impl ours|reference]
+
+N > 1 is launched by ``python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N``
+(one rank per GPU).  Rank 0 prints ONE JSON line.  `value` is device-timed (CUDA events around the
+K steps, max over ranks) with inputs resident on the device; `e2e` repeats the measurement through
+the public API with a pinned-host -> device copy of every step's inputs and a device -> host read of
+the step's loss inside the timed region.  Synthetic data, random-init weights (no network).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--mode", default="async", choices=["async", "sync"])
+    ap.add_argument("--optimizer", default="adagrad")
+    ap.add_argument("--batch", type=int, default=8192, help="examples per rank per step")
+    ap.add_argument("--emb_rows", type=int, default=10_000_000)
+    ap.add_argument("--pool", type=int, default=8, help="distinct synthetic batches cycled through")
+    ap.add_argument("--no_graph", action="store_true", help="do not replay the step as a CUDA graph")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[1]) for r in self.rows if len(r) > 2 and r[1].replace(".", "").isdigit())
+        mx = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = set()
+        for r in self.rows:
+            for n, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def reference_arm(args) -> int:
+    """The unmodified reference is a TensorFlow-1.x script; it can only run where TF imports."""
+    sys.path.insert(0, os.path.join(REPO, "baseline", "_ref"))
+    why = None
+    try:
+        import tensorflow  # noqa: F401
+    except Exception as e:  # noqa: BLE001
+        why = ("reference needs TensorFlow 1.x (tf.app.flags, tf.train.Supervisor, contrib.session_bundle): "
+               "import tensorflow -> %s; no TF wheel in /opt/wheelhouse and none for Python 3.12" % type(e).__name__)
+    if why is None:
+        why = "reference trains a scalar linear model only; it has no wide-and-deep config to time"
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+def main() -> int:
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("gloo", rank=rank, world_size=world)   # host control plane only
+
+    def host_barrier():
+        if world > 1:
+            dist.barrier()
+
+    if args.impl == "torch":
+        from baseline.wide_deep_torch import run_baseline
+        return run_baseline(args, rank, world, dev, ClockSampler)
+
+    from distributed_tensorflow_b200.models.wide_deep import WideDeepConfig, WideDeepTrainer
+    from distributed_tensorflow_b200.ops import _lib
+
+    cfg = WideDeepConfig(emb_rows=args.emb_rows, batch=args.batch, optimizer=args.optimizer, sync=(args.mode == "sync"),
+                         lr=0.05)
+    tr = WideDeepTrainer(cfg, rank=rank, world=world, device=dev)
+    if world > 1:
+        handles = [None] * world
+        dist.all_gather_object(handles, tr.slab_handle())
+        tr.attach_ipc(handles)
+        host_barrier()
+    tr.init_params()
+    torch.cuda.synchronize()
+    host_barrier()
+
+    # synthetic data of the named shape: a pool of pinned host batches + device-resident copies
+    g = torch.Generator().manual_seed(1000 + rank)
+    pool_h = []
+    for _ in range(args.pool):
+        ids = torch.randint(0, cfg.emb_rows, (cfg.batch, cfg.slots), generator=g, dtype=torch.int32).pin_memory()
+        dense = torch.randn(cfg.batch, cfg.dense_in, generator=g).pin_memory()
+        labels = (torch.rand(cfg.batch, generator=g) < 0.25).float().pin_memory()
+        pool_h.append((ids, dense, labels))
+    pool_d = [tuple(t.to(dev) for t in b) for b in pool_h]
+    s_ids, s_dense, s_labels = (torch.empty_like(t, device=dev) for t in pool_h[0])   # static graph inputs
+    loss_host = torch.zeros(1).pin_memory()
+    h2d_bytes = sum(t.numel() * t.element_size() for t in pool_h[0])
+    stream = torch.cuda.Stream(device=dev)
+
+    def load_static(b):
+        s_ids.copy_(b[0], non_blocking=True)
+        s_dense.copy_(b[1], non_blocking=True)
+        s_labels.copy_(b[2], non_blocking=True)
+
+    with torch.cuda.stream(stream):
+        for i in range(max(3, args.warmup)):
+            load_static(pool_d[i % args.pool])
+            tr.step(s_ids, s_dense, s_labels)
+        stream.synchronize()
+        host_barrier()
+        graph = None
+        if not args.no_graph:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=stream):
+                tr.step(s_ids, s_dense, s_labels)
+            graph.replay()
+            stream.synchronize()
+
+        def one_step():
+            if graph is not None:
+                graph.replay()
+            else:
+                tr.step(s_ids, s_dense, s_labels)
+
+        # ---------------- device-timed region: inputs already in HBM ----------------
+        _lib.reset_launch_count()
+        tr.step(s_ids, s_dense, s_labels)          # count the launches of one step outside the graph
+        launches_per_step = _lib.launch_count()
+        stream.synchronize()
+        host_barrier()
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(args.steps):
+            load_static(pool_d[i % args.pool])     # device -> device, keeps every step on fresh ids
+            one_step()
+        e1.record(stream)
+        stream.synchronize()
+        host_barrier()
+        dev_ms = e0.elapsed_time(e1)
+        # ---------------- end-to-end region: pinned host -> device every step, loss read back -----
+        host_barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e2.record(stream)
+        last_loss = 0.0
+        for i in range(args.steps):
+            load_static(pool_h[i % args.pool])     # H2D from pinned memory
+            one_step()
+            loss_host.copy_(tr.last_loss_sum(), non_blocking=True)
+            stream.synchronize()                   # the caller looks at every step's loss
+            last_loss = float(loss_host[0]) / cfg.batch
+        e3.record(stream)
+        stream.synchronize()
+        host_barrier()
+        e2e_ms = e2.elapsed_time(e3)
+        e2e_wall_ms = (time.perf_counter() - t0) * 1e3
+        clocks = sampler.stop() if sampler else None
+
+    t_dev = torch.tensor([dev_ms, max(e2e_ms, e2e_wall_ms)], dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t_dev[0]), float(t_dev[1])
+    global_batch = cfg.batch * world
+    if rank == 0:
+        out = {
+            "metric": "train examples/sec (device-timed, max over ranks)",
+            "value": global_batch * args.steps / (dev_ms / 1e3),
+            "unit": "examples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": dev_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "impl": "ours",
+            "config": {"model": "wide_and_deep 10M x128 embedding + MLP 3392-1024-512-256-1",
+                       "global_batch": global_batch, "per_gpu_batch": cfg.batch, "seq_len": None,
+                       "parallelism": "ps%d (row-sharded embedding + range-sharded dense, every rank worker+ps)" % world,
+                       "mode": args.mode, "optimizer": args.optimizer, "sparse_ids": cfg.slots, "dense_features": cfg.dense_in,
+                       "emb_rows": cfg.emb_rows, "cuda_graph": graph is not None,
+                       "l2": "per-step working set (55 MB gathered operand + random rows of a 2.5 GB table + 54 MB "
+                             "mailbox) exceeds the 126 MB L2; ids change every step"},
+            "e2e": {"value": global_batch * args.steps / (e2e_ms / 1e3), "unit": "examples/s",
+                    "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
+                    "last_loss": last_loss},
+            "gpu_launches": int(launches_per_step) * args.steps,
+            "gpu_launches_per_step": int(launches_per_step),
+            "clocks": clocks,
+        }
+        print(json.dumps(out))
+    tr.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -33,6 +33,27 @@ struct OptConst {
   float beta1, beta2, eps;
 };
 
+// Device-resident step state so that a captured CUDA graph of the step stays valid across replays:
+// the step counter, the per-step optimizer constants and the barrier epoch all live in HBM.
+struct StepState {
+  long long step;          // global_step of this shard (K7: folded into the apply)
+  unsigned int epoch;      // barrier generation
+  unsigned int pad;
+  OptConst oc;
+};
+
+__global__ void wd_tick_kernel(StepState* st, float base_lr, int opt) {
+  const long long t = st->step + 1;
+  st->step = t;
+  OptConst oc;
+  oc.beta1 = 0.9f; oc.beta2 = 0.999f; oc.eps = 1e-8f; oc.lr = base_lr;
+  if (opt == WD_ADAM) {
+    const double b1t = pow(0.9, static_cast<double>(t)), b2t = pow(0.999, static_cast<double>(t));
+    oc.lr = static_cast<float>(base_lr * sqrt(1.0 - b2t) / (1.0 - b1t));
+  }
+  st->oc = oc;
+}
+
 template <int OPT>
 __device__ __forceinline__ void opt_update(float& w, float g, float& s1, float& s2, const OptConst& c) {
   if (OPT == WD_SGD) {
@@ -360,7 +381,8 @@ __global__ void __launch_bounds__(256)
 wd_sparse_apply_rows_kernel(unsigned int* __restrict__ bitmap, long long nwords, float* __restrict__ G,
                             float* __restrict__ wide_G, float* __restrict__ master, float* __restrict__ s1,
                             float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
-                            float* __restrict__ wide_s1, float* __restrict__ wide_s2, OptConst oc) {
+                            float* __restrict__ wide_s1, float* __restrict__ wide_s2, const StepState* __restrict__ stp) {
+  const OptConst oc = stp->oc;
   const int lane = threadIdx.x & 31;
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   for (long long wi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; wi < nwords; wi += nwarps) {
@@ -411,7 +433,8 @@ template <int OPT>
 __global__ void __launch_bounds__(256)
 wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float* __restrict__ s1,
                                float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
-                               float* __restrict__ wide_s1, float* __restrict__ wide_s2, OptConst oc) {
+                               float* __restrict__ wide_s1, float* __restrict__ wide_s2, const StepState* __restrict__ stp) {
+  const OptConst oc = stp->oc;
   __shared__ unsigned int s_prefix[kMaxWorld + 1];
   if (threadIdx.x == 0) {
     unsigned int acc = 0;
@@ -467,8 +490,9 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
 template <int OPT>
 __global__ void __launch_bounds__(256)
 wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, int src_begin, int src_end,
-                      float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2, OptConst oc,
-                      long long small_begin) {
+                      float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2,
+                      const StepState* __restrict__ stp, long long small_begin) {
+  const OptConst oc = stp->oc;
   const long long n4 = (hi - lo) >> 2;
   for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < n4;
        q += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -503,7 +527,14 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
 // Device-side barrier over the signal pads (one 64-byte line per source on every rank).  Thread r
 // optionally publishes how many mailbox entries this rank pushed to rank r, then release-stores
 // `epoch` into rank r's pad and acquire-spins on its own pad until rank r has done the same.
-__global__ void wd_barrier_kernel(PeerTable pt, SlabLayout sl, unsigned int epoch, const unsigned int* publish_cnt) {
+__global__ void wd_barrier_kernel(PeerTable pt, SlabLayout sl, StepState* stp, const unsigned int* publish_cnt) {
+  __shared__ unsigned int s_epoch;
+  if (threadIdx.x == 0) {
+    s_epoch = stp->epoch + 1;
+    stp->epoch = s_epoch;
+  }
+  __syncthreads();
+  const unsigned int epoch = s_epoch;
   const int r = threadIdx.x;
   if (r >= pt.world) return;
   if (publish_cnt != nullptr) reinterpret_cast<unsigned int*>(pt.slab[r] + sl.mbx_count)[pt.rank] = publish_cnt[r];

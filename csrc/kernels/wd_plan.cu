@@ -57,8 +57,8 @@ struct dtf_wd_plan {
   size_t zero_bytes = 0;
   unsigned int *cnt = nullptr, *chunk_counter = nullptr, *tile_flags = nullptr;
   float* loss_acc = nullptr;
-  unsigned int epoch = 0;
-  long long step = 0;
+  StepState* state = nullptr;  // device: step counter, barrier epoch, optimizer constants
+  long long step = 0;          // host mirror of the number of applies issued
 
   template <typename T>
   T* alloc(const char* name, size_t count) {
@@ -86,18 +86,6 @@ static int mask_ld(int n) {
   return w + (w & 1);
 }
 
-static OptConst opt_const(const dtf_wd_plan* p, long long t) {
-  OptConst oc{};
-  oc.beta1 = 0.9f;
-  oc.beta2 = 0.999f;
-  oc.eps = 1e-8f;
-  oc.lr = p->cfg.lr;
-  if (p->cfg.optimizer == WD_ADAM) {
-    const double b1t = pow(0.9, static_cast<double>(t)), b2t = pow(0.999, static_cast<double>(t));
-    oc.lr = static_cast<float>(p->cfg.lr * sqrt(1.0 - b2t) / (1.0 - b1t));
-  }
-  return oc;
-}
 
 extern "C" {
 
@@ -224,6 +212,7 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   const int m_tiles = (sh.B + BM - 1) / BM;
   p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles) * 4;
   ok &= (p->zero_region = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles)) != nullptr;
+  ok &= (p->state = p->alloc<StepState>("step_state", 1)) != nullptr;
   if (!ok) {
     dtf_wd_destroy(p);
     return nullptr;
@@ -449,7 +438,9 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
   mv.count = reinterpret_cast<const unsigned int*>(p->slab + sl.mbx_count);
   mv.cap = p->sh.cap;
   mv.world = p->cfg.world;
-  const OptConst oc = opt_const(p, p->step + 1);
+  const StepState* oc = p->state;
+  wd_tick_kernel<<<1, 1, 0, st>>>(p->state, p->cfg.lr, p->cfg.optimizer);
+  count_launch();
   __nv_bfloat16* work = reinterpret_cast<__nv_bfloat16*>(p->slab + sl.emb_bf16);
   float* wide = reinterpret_cast<float*>(p->slab + sl.wide);
   const int grid = num_sms() * 8;
@@ -520,8 +511,7 @@ int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
       count_launch();
     }
   } else {
-    p->epoch += 1;
-    wd_barrier_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->epoch, publish_counts ? p->cnt : nullptr);
+    wd_barrier_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->state, publish_counts ? p->cnt : nullptr);
     count_launch();
   }
   DTF_CUDA_OK(cudaGetLastError());
