@@ -52,6 +52,24 @@ int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long lo
                   const void* mask_in, void* mask_out, long long ldmask, int splits, int bn,
                   void* stream);
 
+/* Fused parameter pull: H[M,N] = act([gather(row_src) | dense_x] * W^T + bias).  row_src[m*slots+f]
+ * is the device address (local or peer-mapped) of the 128-wide bf16 embedding row of example m,
+ * slot f; gather warps of the same persistent kernel fetch rows over NVLink while its tcgen05
+ * warps multiply row-tiles that already arrived.  The gathered operand stays in a_buf
+ * [M, slots*128 + dense_cols].  scratch: dtf_pull_gemm_scratch_bytes(M) bytes of device memory
+ * owned by the caller (cleared by the call).  Replaces the ps->worker variable read (RecvTensor)
+ * plus the first Mul of reference trainer/task.py:137. */
+size_t dtf_pull_gemm_scratch_bytes(int M);
+int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void* dense_x, int slots, int dense_cols,
+                       void* a_buf, const void* W, long long ldw, const float* bias, void* H, long long ldh,
+                       void* mask_out, long long ldmask, int M, int N, int relu, void* scratch, void* stream);
+
+/* Fused gradient push: dA = dY[M,K] * W[K, :slots*128]; the bf16 row of (m, slot) is stored to the
+ * address row_dst[m*slots+slot] (0 = skip), e.g. a mailbox entry in the owning rank's HBM.
+ * Replaces the worker->ps gradient Send of reference trainer/task.py:138. */
+int dtf_push_gemm_bf16(const void* dY, long long lddy, const void* W, long long ldw,
+                       const unsigned long long* row_dst, int slots, int M, int K, void* stream);
+
 /* ---- symmetric heap (peer-mapped HBM over NVLink / NVSwitch) --------------------------------- *
  * Data plane that replaces the gRPC Send/Recv traffic of every sess.run in the reference
  * (trainer/task.py:236).  Handles are opaque byte strings exchanged by the host control plane. */

@@ -1,0 +1,107 @@
+"""tcgen05 GEMM family vs plain PyTorch fp32: forward / data-gradient / weight-gradient layouts,
+fused epilogues (bias, ReLU + bit-mask, masked dgrad, split-K TMA reduce-add) and the fused
+pull (gather + GEMM) and push (GEMM + row scatter) kernels."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-9)).item()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (300, 200, 136), (1000, 512, 1024), (77, 64, 3392)])
+@pytest.mark.parametrize("bn", [0, 64, 128, 256])
+def test_forward_bias_relu_and_mask(M, N, K, bn):
+    from distributed_tensorflow_b200.ops import gemm as G
+    torch.manual_seed(0)
+    x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    b = torch.randn(N, device="cuda")
+    mask = torch.zeros(M, G.mask_words(N), dtype=torch.int32, device="cuda")
+    y = G.linear_fw(x, w, b, relu=True, bn=bn, mask_out=mask)
+    ref = torch.relu(x.float() @ w.float().t() + b)
+    assert _rel(y, ref) < 1e-2
+    assert torch.equal(G.unpack_mask(mask, N), y > 0)
+    y2 = G.linear_fw(x, w, b, relu=False, bn=bn)
+    assert _rel(y2, x.float() @ w.float().t() + b) < 1e-2
+    y3 = G.linear_fw(x, w, out_dtype=torch.float32, bn=bn)
+    assert _rel(y3, x.float() @ w.float().t()) < 1e-5
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 128), (300, 200, 136), (1000, 512, 1024)])
+def test_data_gradient_with_relu_mask(M, N, K):
+    from distributed_tensorflow_b200.ops import gemm as G
+    torch.manual_seed(1)
+    dy = (torch.randn(M, N, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    keep = torch.rand(M, K, device="cuda") > 0.5
+    for bn in (0, 128, 256):
+        dx = G.linear_dx(dy, w, G.pack_mask(keep), bn=bn)
+        assert _rel(dx, (dy.float() @ w.float()) * keep) < 1e-2
+        assert _rel(G.linear_dx(dy, w, None, bn=bn), dy.float() @ w.float()) < 1e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 256), (256, 200, 136), (2048, 512, 1024)])
+@pytest.mark.parametrize("splits", [1, 0, 7])
+def test_weight_gradient_split_k(M, N, K, splits):
+    from distributed_tensorflow_b200.ops import gemm as G
+    torch.manual_seed(2)
+    dy = (torch.randn(M, N, device="cuda") * 0.5).bfloat16()
+    x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    ref = dy.float().t() @ x.float()
+    assert _rel(G.linear_dw(dy, x, splits=splits), ref) < 1e-4
+    acc = torch.ones(N, K, device="cuda")
+    G.linear_dw(dy, x, out=acc, accumulate=True, splits=splits)          # accumulates into existing values
+    assert _rel(acc, ref + 1) < 1e-4
+
+
+def test_argument_errors_are_reported():
+    from distributed_tensorflow_b200.ops import _lib
+    from distributed_tensorflow_b200.ops import gemm as G
+    x = torch.zeros(128, 72, device="cuda", dtype=torch.bfloat16)[:, :68]      # row stride not 16-byte aligned... ok
+    w = torch.zeros(64, 68, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(_lib.KernelError, match="16-byte"):
+        G.linear_fw(x.contiguous()[:, :67], w[:, :67])
+    with pytest.raises(_lib.KernelError, match="splits"):
+        G.gemm_raw(w, 1, w, 1, torch.zeros(68, 68, device="cuda"), 68, 68, 64, G.EPI_F32, splits=4)
+
+
+@pytest.mark.parametrize("M,slots,dense_cols,N", [(300, 4, 64, 128), (1024, 26, 64, 1024), (128, 2, 0, 256)])
+def test_fused_pull_gemm(M, slots, dense_cols, N):
+    from distributed_tensorflow_b200.ops import fused as F
+    from distributed_tensorflow_b200.ops import gemm as G
+    torch.manual_seed(3)
+    table = (torch.randn(5000, 128, device="cuda") * 0.1).bfloat16()
+    ids = torch.randint(0, 5000, (M, slots), device="cuda")
+    dense = torch.randn(M, dense_cols, device="cuda").bfloat16()
+    K0 = slots * 128 + dense_cols
+    w = (torch.randn(N, K0, device="cuda") * 0.03).bfloat16()
+    b = torch.randn(N, device="cuda") * 0.1
+    mask = torch.zeros(M, G.mask_words(N), dtype=torch.int32, device="cuda")
+    H, a_buf = F.pull_gemm(F.row_addresses(table, ids), dense, w, b, relu=True, mask_out=mask)
+    a_ref = torch.cat([table[ids].reshape(M, slots * 128), dense], dim=1)
+    assert torch.equal(a_buf, a_ref)
+    ref = torch.relu(a_ref.float() @ w.float().t() + b)
+    assert _rel(H, ref) < 1e-2
+    assert torch.equal(G.unpack_mask(mask, N), H > 0)
+
+
+@pytest.mark.parametrize("M,slots,K", [(300, 4, 128), (1024, 26, 1024)])
+def test_fused_push_gemm(M, slots, K):
+    from distributed_tensorflow_b200.ops import fused as F
+    torch.manual_seed(4)
+    dy = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(K, slots * 128 + 64, device="cuda") * 0.05).bfloat16()
+    mailbox = torch.zeros(M * slots + 3, 128, device="cuda", dtype=torch.bfloat16)
+    perm = torch.randperm(M * slots, device="cuda").view(M, slots)
+    dst = (mailbox.data_ptr() + perm * 256).contiguous()
+    dst[5, 1] = 0                                                       # address 0 = this row is not pushed
+    F.push_gemm(dy, w, dst)
+    torch.cuda.synchronize()
+    ref = (dy.float() @ w.float()[:, : slots * 128]).view(M, slots, 128)
+    got = mailbox[perm.view(-1)].view(M, slots, 128).float()
+    ref[5, 1] = 0
+    assert _rel(got, ref) < 1e-2
+    assert mailbox[M * slots:].abs().max() == 0
