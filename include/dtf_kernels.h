@@ -70,6 +70,22 @@ int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void* dense_x, i
 int dtf_push_gemm_bf16(const void* dY, long long lddy, const void* W, long long ldw,
                        const unsigned long long* row_dst, int slots, int M, int K, void* stream);
 
+/* Same computation as dtf_pull_gemm_bf16 for callers that cannot allocate device memory (a process
+ * whose device memory was all handed to its own pool at start-up, a plug-in inside one, or a
+ * request path that cannot tolerate cudaMalloc's device-wide synchronisation): the scratch is a
+ * static device array inside the library (about 32 KiB per GPU that loads the library, held until
+ * exit), so there is no scratch argument and M is limited to dtf_pull_gemm_noalloc_max_rows()
+ * (1,048,576); larger M is rejected with an error.  The call allocates nothing.  All calls on a
+ * device share that array, which keeps the previous call's contents (the used part is cleared at the
+ * start of each call): calls whose GPU work overlaps race -- keep them stream-ordered.  The first
+ * call on each device resolves the array's device address; issue it at start-up, before any stream
+ * capture.  This entry point has no counterpart in the reference. */
+int dtf_pull_gemm_noalloc_max_rows(void);
+int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, const void* dense_x, int slots,
+                               int dense_cols, void* a_buf, const void* W, long long ldw, const float* bias,
+                               void* H, long long ldh, void* mask_out, long long ldmask, int M, int N,
+                               int relu, void* stream);
+
 /* ---- symmetric heap (peer-mapped HBM over NVLink / NVSwitch) --------------------------------- *
  * Data plane that replaces the gRPC Send/Recv traffic of every sess.run in the reference
  * (trainer/task.py:236).  Handles are opaque byte strings exchanged by the host control plane. */
