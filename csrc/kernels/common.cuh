@@ -15,8 +15,12 @@ int num_sms();
 
 // 2-D bf16 tensor map with 128-byte swizzle.  `inner` is the contiguous dimension.
 // Returns false (and sets the error string) on failure.
-bool make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes /*2=bf16, 4=f32*/, uint64_t inner,
-                  uint64_t outer, uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer);
+bool make_tmap_2d_ex(CUtensorMap* out, const void* base, int elem_bytes /*2=bf16, 4=f32*/, uint64_t inner,
+                     uint64_t outer, uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, bool swizzle128);
+inline bool make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t outer,
+                         uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer) {
+  return make_tmap_2d_ex(out, base, elem_bytes, inner, outer, row_stride_bytes, box_inner, box_outer, true);
+}
 inline bool make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
                               uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer) {
   return make_tmap_2d(out, base, 2, inner, outer, row_stride_bytes, box_inner, box_outer);

@@ -30,7 +30,7 @@ struct GemmArgs {
 
 template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
 int launch_gemm_t(const GemmArgs& a) {
-  using S = GemmSmem<BN>;
+  using S = GemmSmem<BN, GATHER>;
   auto kern = gemm_sm100_kernel<BN, A_MN, B_MN, EPI, GATHER>;
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -80,7 +80,7 @@ int launch_gemm_t(const GemmArgs& a) {
   p.row_dst = a.row_dst;
   const int tiles = p.m_tiles * p.n_tiles * p.splits;
   int grid = tiles < num_sms() ? tiles : num_sms();
-  if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of idle CTAs still pull rows
+  if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of CTAs without tiles still pull rows
   const int threads = GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads;
   kern<<<grid, threads, S::kTotal, a.stream>>>(tmA, tmB, tmD, p);
   DTF_CUDA_OK(cudaGetLastError());

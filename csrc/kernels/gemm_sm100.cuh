@@ -25,7 +25,10 @@ constexpr int BM = 128;       // rows per CTA tile == UMMA M
 constexpr int BK = 64;        // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;    // fixed for 16-bit inputs
 constexpr int kNumMainThreads = 192;
-constexpr int kNumGatherThreads = 128;
+constexpr int kNumGatherWarps = 6;
+constexpr int kNumGatherThreads = kNumGatherWarps * 32;
+constexpr int kSliceRows = 16;          // rows per gather slice (one warp, 8 x LDG.128 per lane)
+constexpr int kSlicesPerTile = BM / kSliceRows;
 
 enum Epilogue : int {
   EPI_BF16 = 0,            // D = bf16(acc)
@@ -53,23 +56,25 @@ struct GemmParams {
   long long lda_buf;
   int slots;                          // F
   int dense_cols;                     // 64
-  unsigned int* tile_flags;           // [m_tiles] arrival counters, zero before launch
-  unsigned int* chunk_counter;        // [1] dynamic chunk claim, zero before launch
+  unsigned int* tile_flags;           // [m_tiles] arrival counters (8*(slots+1) slices each), zero before launch
+  unsigned int* chunk_counter;        // [1] reserved
   // --- fused push epilogue: destination of the 128-wide bf16 row for (m, slot) ---
   const unsigned long long* row_dst;  // [M * slots] global addresses (may be peer mailbox)
 };
 
-template <int BN>
+template <int BN, bool GATHER = false>
 struct GemmSmem {
   static constexpr int kABytes = BM * BK * 2;  // 16 KB
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 4 : ((BN == 128) ? 6 : 8);
+  static constexpr int kGatherBytes = 0;
   static constexpr int kStagingPerWarp = 5120;  // 32 rows x 128 B (TMA store) or x 144 B (push)
   static constexpr int kStagingBytes = 4 * kStagingPerWarp;
   static constexpr int kBarBytes = 256;
   static constexpr int kBiasBytes = BN * 4 * 2;
-  static constexpr int kTotal = kStages * kStageBytes + kStagingBytes + kBarBytes + kBiasBytes + 1024 /*align*/;
+  static constexpr int kTotal =
+      kStages * kStageBytes + kStagingBytes + kGatherBytes + kBarBytes + kBiasBytes + 1024 /*align*/;
 };
 
 // tile index -> (m, n, split); n fastest so that concurrently running CTAs share A row-tiles.
@@ -85,7 +90,7 @@ template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
 __global__ void __launch_bounds__(GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
-  using S = GemmSmem<BN>;
+  using S = GemmSmem<BN, GATHER>;
   constexpr int kStages = S::kStages;
   constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : 2 * BN;  // two accumulator buffers
   constexpr bool kOutF32 = (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC);
@@ -98,14 +103,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                                              ~static_cast<uintptr_t>(1023));
   const uint32_t smem_base = smem_u32(smem);
   const uint32_t staging_base = smem_base + kStages * S::kStageBytes;  // 1024-aligned
-  const uint32_t bar_base = staging_base + S::kStagingBytes;
+  const uint32_t gather_base = staging_base + S::kStagingBytes;      // 1024-aligned
+  const uint32_t bar_base = gather_base + S::kGatherBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * kStages + b); };
   auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * kStages + 2 + b); };
-  uint8_t* misc = smem + kStages * S::kStageBytes + S::kStagingBytes;
+  uint8_t* misc = smem + kStages * S::kStageBytes + S::kStagingBytes + S::kGatherBytes;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(misc + 8 * (2 * kStages + 4));
-  int* claimed = reinterpret_cast<int*>(misc + 8 * (2 * kStages + 4) + 8);
   float* bias_smem = reinterpret_cast<float*>(misc + S::kBarBytes);
 
   const int warp = threadIdx.x >> 5;
@@ -147,12 +152,17 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int kb1 = min(total_kb, kb0 + p.k_blocks_per_split);
         if constexpr (GATHER) {
           // wait until every chunk of this row-tile has been gathered into a_buf
-          const unsigned int need = static_cast<unsigned int>(p.slots + 1);
+          // relaxed polling with back-off (an acquire load per poll would flush L1 every time), then
+          // one acquire fence and the generic->async proxy fence before TMA reads the rows
+          const unsigned int need = static_cast<unsigned int>(kSlicesPerTile * (p.slots + 1));
           unsigned int v;
-          do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.tile_flags + m_t) : "memory");
-          } while (v < need);
-          asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA reads
+          for (;;) {
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.tile_flags + m_t) : "memory");
+            if (v >= need) break;
+            __nanosleep(64);
+          }
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");
+          asm volatile("fence.proxy.async;" ::: "memory");
         }
         for (int kb = kb0; kb < kb1; ++kb, ++kiter) {
           const int s = kiter % kStages;
@@ -339,62 +349,88 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tma_store_wait_all();
   } else {
     // =============================== gather warps (fused pull) ===============================
+    // Six independent warps, no shared memory and no intra-CTA synchronisation.  The work is cut
+    // into slices of 16 rows x one slot (4 KB): a warp loads the 16 row addresses, issues 8
+    // LDG.128 per lane straight from the owning rank's HBM (local, or a peer's over NVLink),
+    // stores them into the GEMM operand buffer and bumps the row-tile's arrival counter.  Two
+    // slices are processed together so that 16 x 16 B per lane (8 KB per warp, 48 KB per SM) are in
+    // flight -- enough to cover NVLink latency at link rate.  Slices are dealt round-robin over all
+    // gather warps of the grid in row-tile order, so row-tiles complete in the order the MMA warps
+    // consume them.  (Needs every CTA resident: grid <= SM count, one CTA per SM.)
     if constexpr (GATHER) {
-      const int gt = threadIdx.x - kNumMainThreads;  // 0..127
+      const int gw = warp - 6;
       const int chunks_per_tile = p.slots + 1;
-      const int total_chunks = p.m_tiles * chunks_per_tile;
-      for (;;) {
-        if (gt == 0) *claimed = static_cast<int>(atomicAdd(p.chunk_counter, 1u));
-        named_bar_sync(2, kNumGatherThreads);
-        const int chunk = *claimed;
-        named_bar_sync(3, kNumGatherThreads);
-        if (chunk >= total_chunks) break;
-        const int m_t = chunk / chunks_per_tile;
-        const int f = chunk % chunks_per_tile;
-        const int row0 = m_t * BM;
-        if (f < p.slots) {
-          // 128 rows x 256 B = 2048 16-byte pieces; 16 per thread, 8 loads in flight at a time
+      const long long total_slices = static_cast<long long>(p.m_tiles) * chunks_per_tile * kSlicesPerTile;
+      const long long stride = static_cast<long long>(gridDim.x) * kNumGatherWarps;
+      const int dense_pieces = p.dense_cols / 8;  // 16-byte pieces per dense row
+      for (long long s0 = static_cast<long long>(blockIdx.x) * kNumGatherWarps + gw; s0 < total_slices; s0 += 2 * stride) {
+        uint4 v[2][8];
+        int mt[2];
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint4 v[8];
-            bool ok[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const int piece = (half * 8 + u) * kNumGatherThreads + gt;
-              const int r = row0 + (piece >> 4);
-              ok[u] = r < p.M;
-              if (ok[u]) {
-                const unsigned long long src = __ldg(p.row_src + static_cast<long long>(r) * p.slots + f);
-                v[u] = ld_global_nc_v4(reinterpret_cast<const uint8_t*>(src) + (piece & 15) * 16);
-              }
-            }
+        for (int h = 0; h < 2; ++h) {
+          const long long sl = s0 + h * stride;
+          mt[h] = -1;
+          if (sl >= total_slices) continue;
+          const int chunk = static_cast<int>(sl / kSlicesPerTile), part = static_cast<int>(sl % kSlicesPerTile);
+          const int m_t = chunk / chunks_per_tile, f = chunk % chunks_per_tile;
+          mt[h] = m_t;
+          const int row0 = m_t * BM + part * kSliceRows;
+          if (f < p.slots) {
+            // lanes 0..15 fetch the 16 row addresses once; every step broadcasts the one it needs,
+            // so the eight 16-byte row loads of a lane are issued back to back
+            unsigned long long my_src = 0ull;
+            if (lane < kSliceRows && row0 + lane < p.M)
+              my_src = __ldg(p.row_src + static_cast<long long>(row0 + lane) * p.slots + f);
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
-              const int piece = (half * 8 + u) * kNumGatherThreads + gt;
-              const int r = row0 + (piece >> 4);
-              if (ok[u]) {
-                uint8_t* d = reinterpret_cast<uint8_t*>(p.a_buf + static_cast<long long>(r) * p.lda_buf + f * 128) +
-                             (piece & 15) * 16;
-                st_global_v4(d, v[u].x, v[u].y, v[u].z, v[u].w);
-              }
+              const int pc = u * 32 + lane;
+              const unsigned long long src = __shfl_sync(0xffffffffu, my_src, pc >> 4);
+              if (src != 0ull) v[h][u] = ld_global_nc_v4(reinterpret_cast<const uint8_t*>(src) + (pc & 15) * 16);
             }
-          }
-        } else {
-          // dense feature block: dense_cols bf16 per row, local copy
-          const int pieces_per_row = p.dense_cols / 8;
-          for (int piece = gt; piece < BM * pieces_per_row; piece += kNumGatherThreads) {
-            const int r = row0 + piece / pieces_per_row;
-            const int c = piece % pieces_per_row;
-            if (r < p.M) {
-              uint4 v = ld_global_nc_v4(p.dense_x + static_cast<long long>(r) * p.dense_cols + c * 8);
-              st_global_v4(p.a_buf + static_cast<long long>(r) * p.lda_buf + p.slots * 128 + c * 8, v.x, v.y, v.z, v.w);
+          } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int pc = u * 32 + lane;
+              const int r = row0 + pc / dense_pieces;
+              if (pc < kSliceRows * dense_pieces && r < p.M)
+                v[h][u] = ld_global_nc_v4(p.dense_x + static_cast<long long>(r) * p.dense_cols + (pc % dense_pieces) * 8);
             }
           }
         }
-        __threadfence();
-        named_bar_sync(2, kNumGatherThreads);
-        if (gt == 0) {
-          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.tile_flags + m_t) : "memory");
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const long long sl = s0 + h * stride;
+          if (sl >= total_slices) continue;
+          const int chunk = static_cast<int>(sl / kSlicesPerTile), part = static_cast<int>(sl % kSlicesPerTile);
+          const int m_t = chunk / chunks_per_tile, f = chunk % chunks_per_tile;
+          const int row0 = m_t * BM + part * kSliceRows;
+          if (f < p.slots) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const int pc = u * 32 + lane;
+              const int r = row0 + (pc >> 4);
+              if (r < p.M)
+                st_global_v4(reinterpret_cast<uint8_t*>(p.a_buf + static_cast<long long>(r) * p.lda_buf + f * 128) + (pc & 15) * 16,
+                             v[h][u].x, v[h][u].y, v[h][u].z, v[h][u].w);
+            }
+          } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int pc = u * 32 + lane;
+              const int r = row0 + pc / dense_pieces;
+              if (pc < kSliceRows * dense_pieces && r < p.M)
+                st_global_v4(p.a_buf + static_cast<long long>(r) * p.lda_buf + p.slots * 128 + (pc % dense_pieces) * 8,
+                             v[h][u].x, v[h][u].y, v[h][u].z, v[h][u].w);
+            }
+          }
+        }
+        // __syncwarp orders the lanes' stores before lane 0's release, which is cumulative
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            if (mt[h] >= 0)
+              asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.tile_flags + mt[h]) : "memory");
         }
       }
     }

@@ -95,6 +95,17 @@ __device__ __forceinline__ void bulk_store_1d(void* dst_global, uint32_t src_sme
                "r"(bytes)
                : "memory");
 }
+// 1-D bulk copy global (local or peer-mapped) -> smem, completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst_smem, const void* src_global, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
+               "l"(src_global), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// wait until at most N of this thread's bulk groups are still pending (writes complete, not just reads)
+template <int N>
+__device__ __forceinline__ void tma_store_wait_pending() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
 __device__ __forceinline__ void tma_store_wait_all() {
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }

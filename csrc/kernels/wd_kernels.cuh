@@ -293,34 +293,43 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------ colsum
-// out[n] += sum_m x[m, n]  (bias gradients).  Block = 64 columns x `rows_per_block` rows.
+// out[n] += sum_m x[m, n]  (bias gradients).  Block = 256 columns x `rows_per_block` rows; every
+// thread streams 8 columns (one 16-byte load per row) for one of 8 row groups.
 __global__ void __launch_bounds__(256)
 wd_colsum_kernel(const __nv_bfloat16* __restrict__ x, int M, int N, long long ld, int rows_per_block,
                  float* __restrict__ out) {
-  __shared__ float s[8][64];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int col = blockIdx.x * 64 + lane * 2;
+  __shared__ float s[8][256];
+  const int cg = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + cg * 8;
   const int r0 = blockIdx.y * rows_per_block;
   const int r1 = min(M, r0 + rows_per_block);
-  float a = 0.f, b = 0.f;
-  if (col < N) {
-    for (int r = r0 + warp; r < r1; r += 8) {
-      const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(x + static_cast<long long>(r) * ld + col);
-      const float2 f = __bfloat1622float2(v);
-      a += f.x;
-      b += f.y;
-    }
-  }
-  s[warp][lane * 2] = a;
-  s[warp][lane * 2 + 1] = b;
-  __syncthreads();
-  if (threadIdx.x < 64) {
-    float t = 0.f;
+  float acc[8];
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += s[w][threadIdx.x];
-    const int c = blockIdx.x * 64 + threadIdx.x;
-    if (c < N) atomicAdd(out + c, t);
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (col + 8 <= N) {
+#pragma unroll 4
+    for (int r = r0 + rg; r < r1; r += 8) {
+      const uint4 raw = ld_global_nc_v4(x + static_cast<long long>(r) * ld + col);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __bfloat1622float2(h[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+  } else if (col < N) {
+    for (int r = r0 + rg; r < r1; r += 8)
+      for (int j = 0; j < 8 && col + j < N; ++j) acc[j] += __bfloat162float(x[static_cast<long long>(r) * ld + col + j]);
   }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[rg][cg * 8 + j] = acc[j];
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) t += s[w][threadIdx.x];
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < N) atomicAdd(out + c, t);
 }
 
 // ------------------------------------------------------------------------------------------ sparse
@@ -448,37 +457,59 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
   const long long total = s_prefix[mv.world];
   const int lane = threadIdx.x & 31;
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += nwarps) {
-    long long e;
-    if (!mailbox_locate(mv, s_prefix, gi, e)) continue;
-    const long long row = mv.rows[e];
-    const long long o = row * kEmbDim + lane * 4;
-    const uint2 raw = *reinterpret_cast<const uint2*>(mv.payload + e * kEmbDim + lane * 4);
-    const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
-    const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
-    float4 w = *reinterpret_cast<float4*>(master + o);
-    float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
-    if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + o);
-    if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + o);
-    opt_update<OPT>(w.x, ga.x, a.x, v.x, oc);
-    opt_update<OPT>(w.y, ga.y, a.y, v.y, oc);
-    opt_update<OPT>(w.z, gb.x, a.z, v.z, oc);
-    opt_update<OPT>(w.w, gb.y, a.w, v.w, oc);
-    *reinterpret_cast<float4*>(master + o) = w;
-    if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o) = a;
-    if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o) = v;
-    uint2 pk;
-    pk.x = pack_bf16x2(w.x, w.y);
-    pk.y = pack_bf16x2(w.z, w.w);
-    *reinterpret_cast<uint2*>(work + o) = pk;
-    if (lane == 0) {
-      float ww = wide[row], wa = 0.f, wv = 0.f;
-      if (OPT != WD_SGD) wa = wide_s1[row];
-      if (OPT == WD_ADAM) wv = wide_s2[row];
-      opt_update<OPT>(ww, mv.dl[e], wa, wv, oc);
-      wide[row] = ww;
-      if (OPT != WD_SGD) wide_s1[row] = wa;
-      if (OPT == WD_ADAM) wide_s2[row] = wv;
+  // two entries per iteration: both rows' loads are in flight before either is updated
+  for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += 2 * nwarps) {
+    long long e[2], row[2] = {0, 0}, o[2] = {0, 0};
+    bool ok[2];
+    uint2 raw[2];
+    float4 w[2], a[2], v[2];
+    float dlv[2], ww[2], wa[2], wv[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long long g = gi + u * nwarps;
+      ok[u] = g < total && mailbox_locate(mv, s_prefix, g, e[u]);
+      if (ok[u]) row[u] = mv.rows[e[u]];
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      a[u] = make_float4(0, 0, 0, 0);
+      v[u] = make_float4(0, 0, 0, 0);
+      wa[u] = wv[u] = 0.f;
+      if (!ok[u]) continue;
+      o[u] = row[u] * kEmbDim + lane * 4;
+      raw[u] = *reinterpret_cast<const uint2*>(mv.payload + e[u] * kEmbDim + lane * 4);
+      w[u] = *reinterpret_cast<float4*>(master + o[u]);
+      if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
+      if (OPT == WD_ADAM) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
+      if (lane == 0) {
+        dlv[u] = mv.dl[e[u]];
+        ww[u] = wide[row[u]];
+        if (OPT != WD_SGD) wa[u] = wide_s1[row[u]];
+        if (OPT == WD_ADAM) wv[u] = wide_s2[row[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (!ok[u]) continue;
+      const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].x));
+      const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].y));
+      opt_update<OPT>(w[u].x, ga.x, a[u].x, v[u].x, oc);
+      opt_update<OPT>(w[u].y, ga.y, a[u].y, v[u].y, oc);
+      opt_update<OPT>(w[u].z, gb.x, a[u].z, v[u].z, oc);
+      opt_update<OPT>(w[u].w, gb.y, a[u].w, v[u].w, oc);
+      *reinterpret_cast<float4*>(master + o[u]) = w[u];
+      if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o[u]) = a[u];
+      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
+      uint2 pk;
+      pk.x = pack_bf16x2(w[u].x, w[u].y);
+      pk.y = pack_bf16x2(w[u].z, w[u].w);
+      *reinterpret_cast<uint2*>(work + o[u]) = pk;
+      if (lane == 0) {
+        opt_update<OPT>(ww[u], dlv[u], wa[u], wv[u], oc);
+        wide[row[u]] = ww[u];
+        if (OPT != WD_SGD) wide_s1[row[u]] = wa[u];
+        if (OPT == WD_ADAM) wide_s2[row[u]] = wv[u];
+      }
     }
   }
 }

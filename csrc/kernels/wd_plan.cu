@@ -8,6 +8,7 @@
 
 #include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/dtf_kernels.h"
@@ -57,6 +58,9 @@ struct dtf_wd_plan {
   size_t zero_bytes = 0;
   unsigned int *cnt = nullptr, *chunk_counter = nullptr, *tile_flags = nullptr;
   float* loss_acc = nullptr;
+  // optional per-kernel tracing: CUDA events recorded between launches
+  bool profile = false;
+  std::vector<std::pair<std::string, cudaEvent_t>> marks;
   StepState* state = nullptr;  // device: step counter, barrier epoch, optimizer constants
   long long step = 0;          // host mirror of the number of applies issued
 
@@ -80,6 +84,14 @@ struct dtf_wd_plan {
     return reinterpret_cast<T*>(slab + off);
   }
 };
+
+static void mark(dtf_wd_plan* p, cudaStream_t st, const char* name) {
+  if (!p->profile) return;
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  cudaEventRecord(e, st);
+  p->marks.emplace_back(name, e);
+}
 
 static int mask_ld(int n) {
   int w = (n + 31) / 32;
@@ -338,6 +350,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   const int n = static_cast<int>(sh.cap);
+  mark(p, st, "begin");
   DTF_CUDA_OK(cudaMemsetAsync(p->zero_region, 0, p->zero_bytes, st));
   wd_route_kernel<<<(n + 255) / 256, 256, 0, st>>>(ids, n, sh.V, p->pt, p->sl, sh.cap, p->cnt, p->row_src, p->wide_src,
                                                    p->row_dst, p->dl_dst);
@@ -345,6 +358,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
                                                                          sh.dense_pad);
   DTF_CUDA_OK(cudaGetLastError());
   count_launch(2);
+  mark(p, st, "route+pad");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
   // layer 1: embedding pull fused with the GEMM
@@ -355,6 +369,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
   a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
   if (launch_gemm_gather(a) != 0) return -1;
+  mark(p, st, "pull+gemm1");
   // layers 2, 3
   a = base_args(st);
   a.A = p->H1; a.lda = sh.h1; a.B = W + dl.w2; a.ldb = sh.h1; a.D = p->H2; a.ldd = sh.h2;
@@ -366,6 +381,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.M = sh.B; a.N = sh.h3; a.K = sh.h2; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b3 - dl.small_begin);
   a.mask_out = train ? p->m3 : nullptr; a.ldmask = p->ldm3;
   if (launch_gemm_kk(a) != 0) return -1;
+  mark(p, st, "gemm2+gemm3");
   return 0;
 }
 
@@ -420,8 +436,8 @@ static int dgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n, const __nv_bflo
 }
 
 static int colsum(const __nv_bfloat16* x, int M, int N, float* out, cudaStream_t st) {
-  const int rpb = 256;
-  dim3 grid((N + 63) / 64, (M + rpb - 1) / rpb);
+  const int rpb = 128;
+  dim3 grid((N + 255) / 256, (M + rpb - 1) / rpb);
   wd_colsum_kernel<<<grid, 256, 0, st>>>(x, M, N, N, rpb, out);
   DTF_CUDA_OK(cudaGetLastError());
   count_launch();
@@ -446,13 +462,16 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
   const int grid = num_sms() * 8;
   if (p->cfg.sync) {
     wd_sparse_accum_kernel<<<grid, 256, 0, st>>>(mv, p->G, p->wide_G, p->bitmap);
+    mark(p, st, "sparse accum");
     wd_sparse_apply_rows_kernel<OPT><<<grid, 256, 0, st>>>(p->bitmap, p->bitmap_words, p->G, p->wide_G, p->emb_master,
                                                            p->emb_s1, p->emb_s2, work, wide, p->wide_s1, p->wide_s2, oc);
     count_launch(2);
+    mark(p, st, "sparse apply rows");
   } else {
     wd_sparse_apply_entries_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
                                                               p->wide_s1, p->wide_s2, oc);
     count_launch();
+    mark(p, st, "sparse apply entries");
   }
   if (p->cfg.sync) {
     wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, 0, p->cfg.world,
@@ -468,11 +487,36 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
       count_launch();
     }
   }
+  mark(p, st, "dense apply");
   DTF_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 extern "C" {
+
+// Tracing: with profiling on, every executor call records CUDA events between its launches;
+// dtf_wd_profile_read synchronises, writes "name=microseconds" lines (time since the previous mark)
+// into buf and clears the marks.  Not for use under CUDA-graph capture.
+void dtf_wd_profile_enable(dtf_wd_plan* p, int on) { p->profile = on != 0; }
+int dtf_wd_profile_read(dtf_wd_plan* p, char* buf, size_t cap) {
+  cudaDeviceSynchronize();
+  std::string out;
+  for (size_t i = 1; i < p->marks.size(); ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, p->marks[i - 1].second, p->marks[i].second);
+    char line[128];
+    snprintf(line, sizeof(line), "%s=%.1f\n", p->marks[i].first.c_str(), ms * 1e3f);
+    out += line;
+  }
+  for (auto& m : p->marks) cudaEventDestroy(m.second);
+  p->marks.clear();
+  if (buf && cap) {
+    const size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+  }
+  return static_cast<int>(out.size());
+}
 
 // forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
 // [B*dense_in], labels f32 [B]
@@ -480,25 +524,34 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
+  mark(p, st, "step");
   DTF_CUDA_OK(cudaMemsetAsync(p->slab + p->sl.dense_grad, 0, static_cast<size_t>(p->P_pad) * 4, st));
   if (forward(p, ids, dense_raw, st, true) != 0) return -1;
   if (launch_loss(p, labels, st, true) != 0) return -1;
+  mark(p, st, "loss+wide");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
   if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
+  mark(p, st, "wgrad3");
   if (dgrad(p, p->dZ3, sh.h3, W + dl.w3, sh.h2, p->m2, p->ldm2, p->dZ2, st) != 0) return -1;
+  mark(p, st, "dgrad3");
   if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
+  mark(p, st, "wgrad2");
   if (dgrad(p, p->dZ2, sh.h2, W + dl.w2, sh.h1, p->m1, p->ldm1, p->dZ1, st) != 0) return -1;
+  mark(p, st, "dgrad2");
   if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st) != 0) return -1;
+  mark(p, st, "wgrad1");
   if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
   if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
   if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
+  mark(p, st, "colsum x3");
   // fused push: dA = dZ1 W1[:, :F*128]; every 128-wide row goes to its owner's mailbox
   GemmArgs a = base_args(st);
   a.A = p->dZ1; a.lda = sh.h1; a.B = W + dl.w1; a.ldb = sh.K0; a.b_mn = true;
   a.M = sh.B; a.N = sh.F * kEmbDim; a.K = sh.h1; a.epi = EPI_PUSH_ROWS; a.row_dst = p->row_dst; a.slots = sh.F;
   a.bn = 256;
   if (launch_gemm_kmn(a) != 0) return -1;
+  mark(p, st, "dgrad1+push");
   return 0;
 }
 
@@ -514,6 +567,7 @@ int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
     wd_barrier_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->state, publish_counts ? p->cnt : nullptr);
     count_launch();
   }
+  mark(p, st, "barrier");
   DTF_CUDA_OK(cudaGetLastError());
   return 0;
 }

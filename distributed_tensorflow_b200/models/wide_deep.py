@@ -233,6 +233,23 @@ class WideDeepTrainer:
         _lib.check(self._L.dtf_wd_predict(self._h, a, b, self._stream()), "dtf_wd_predict")
         return self.buffer("prob", torch.float32)
 
+    def profile(self, on: bool) -> None:
+        """Per-kernel tracing: CUDA events between the launches of every executor call."""
+        self._L.dtf_wd_profile_enable.restype = None
+        self._L.dtf_wd_profile_enable.argtypes = [C.c_void_p, C.c_int]
+        self._L.dtf_wd_profile_enable(self._h, int(on))
+
+    def profile_read(self) -> List[tuple]:
+        """[(kernel group, microseconds), ...] since the last read (synchronises the device)."""
+        self._L.dtf_wd_profile_read.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
+        buf = C.create_string_buffer(1 << 16)
+        self._L.dtf_wd_profile_read(self._h, buf, len(buf))
+        out = []
+        for line in buf.value.decode().splitlines():
+            k, _, v = line.rpartition("=")
+            out.append((k, float(v)))
+        return out
+
     def last_loss_sum(self) -> torch.Tensor:
         """Device scalar: sum over the micro-batch of the per-example loss of the last step."""
         return self.loss_view

@@ -148,6 +148,9 @@ int dtf_wd_step(dtf_wd_plan*, const int* ids, const float* dense, const float* l
 int dtf_wd_predict(dtf_wd_plan*, const int* ids, const float* dense, void* stream);
 int dtf_wd_read_loss(dtf_wd_plan*, float* loss_sum, void* stream);
 void* dtf_wd_loss_ptr(dtf_wd_plan*);
+/* per-kernel tracing with CUDA events (the reference only prints wall-clock, trainer/task.py:100-102) */
+void dtf_wd_profile_enable(dtf_wd_plan*, int on);
+int dtf_wd_profile_read(dtf_wd_plan*, char* buf, size_t cap);
 
 #ifdef __cplusplus
 }
