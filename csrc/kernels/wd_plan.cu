@@ -349,7 +349,7 @@ static GemmArgs base_args(cudaStream_t st) {
 static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaStream_t st, bool train) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
-  const int n = static_cast<int>(sh.cap);
+  const int n = sh.B * sh.F;
   mark(p, st, "begin");
   DTF_CUDA_OK(cudaMemsetAsync(p->zero_region, 0, p->zero_bytes, st));
   wd_route_kernel<<<(n + 255) / 256, 256, 0, st>>>(ids, n, sh.V, p->pt, p->sl, sh.cap, p->cnt, p->row_src, p->wide_src,
@@ -593,11 +593,21 @@ int dtf_wd_step(dtf_wd_plan* p, const int* ids, const float* dense_raw, const fl
   return 0;
 }
 
-// serving / evaluation forward: probabilities for B examples into the plan's "prob" buffer
-int dtf_wd_predict(dtf_wd_plan* p, const int* ids, const float* dense_raw, void* stream_) {
+// serving / evaluation forward: probabilities of the first n examples (n <= batch) into the plan's
+// "prob" buffer.  Small n takes the small-M path of the same kernels: one 128-row tile, TMA
+// zero-fill for the missing rows.
+int dtf_wd_predict(dtf_wd_plan* p, const int* ids, const float* dense_raw, int n, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
-  if (forward(p, ids, dense_raw, st, false) != 0) return -1;
-  return launch_loss(p, nullptr, st, false);
+  if (n < 1 || n > p->cfg.batch) {
+    set_error("dtf_wd_predict: n=%d outside [1, %d]", n, p->cfg.batch);
+    return -2;
+  }
+  const int full = p->sh.B;
+  p->sh.B = n;
+  int rc = forward(p, ids, dense_raw, st, false);
+  if (rc == 0) rc = launch_loss(p, nullptr, st, false);
+  p->sh.B = full;
+  return rc;
 }
 
 // sum of per-example losses of the last step (device -> host, synchronises the stream)

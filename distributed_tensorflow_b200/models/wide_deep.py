@@ -99,7 +99,7 @@ def _bind(L):
         fn.argtypes = [vp, vp, vp, vp, vp]
     L.dtf_wd_barrier.argtypes = [vp, i, vp]
     L.dtf_wd_step_apply.argtypes = [vp, vp]
-    L.dtf_wd_predict.argtypes = [vp, vp, vp, vp]
+    L.dtf_wd_predict.argtypes = [vp, vp, vp, i, vp]
     L.dtf_wd_read_loss.argtypes = [vp, C.POINTER(C.c_float), vp]
     L.dtf_wd_loss_ptr.restype = vp
     L.dtf_wd_loss_ptr.argtypes = [vp]
@@ -228,10 +228,55 @@ class WideDeepTrainer:
     def step_apply(self) -> None:
         _lib.check(self._L.dtf_wd_step_apply(self._h, self._stream()), "dtf_wd_step_apply")
 
-    def predict(self, ids: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
-        a, b, _ = self._ptrs(ids, dense)
-        _lib.check(self._L.dtf_wd_predict(self._h, a, b, self._stream()), "dtf_wd_predict")
-        return self.buffer("prob", torch.float32)
+    def predict(self, ids: torch.Tensor, dense: torch.Tensor, n: Optional[int] = None) -> torch.Tensor:
+        """Probabilities for the first ``n`` examples (default: a full batch).  ``ids`` / ``dense`` may
+        hold just ``n`` rows; the result is a view of the plan's ``prob`` buffer."""
+        n = int(n if n is not None else ids.shape[0])
+        assert ids.dtype == torch.int32 and ids.is_cuda and ids.is_contiguous() and ids.numel() >= n * self.cfg.slots
+        assert dense.dtype == torch.float32 and dense.is_contiguous() and dense.numel() >= n * self.cfg.dense_in
+        _lib.check(self._L.dtf_wd_predict(self._h, C.c_void_p(ids.data_ptr()), C.c_void_p(dense.data_ptr()), n,
+                                          self._stream()), "dtf_wd_predict")
+        return self.buffer("prob", torch.float32)[:n]
+
+    # ------------------------------------------------------------------ parameter-server shard state
+    _SLOT_NAMES = {"adagrad": ("Adagrad",), "adam": ("Adam", "Adam_1"), "sgd": ()}
+
+    def named_shards(self) -> Dict[str, torch.Tensor]:
+        """This rank's ps shard as named device tensors (fp32 masters + optimizer slots), using the
+        ``<variable>/part_<rank>`` convention for partitioned variables and TF slot names."""
+        c, r = self.cfg, self.rank
+        n = self.info.rows_local
+        out = {"embedding/part_%d" % r: self.buffer("emb_master", torch.float32)[: n * c.emb_dim].view(n, c.emb_dim),
+               "wide_weights/part_%d" % r: self.buffer("wide", torch.float32)[:n],
+               "dense_flat/part_%d" % r: self.buffer("dense_master", torch.float32)}
+        for i, slot in enumerate(self._SLOT_NAMES[c.optimizer]):
+            k = "slot%d" % (i + 1)
+            out["embedding/part_%d/%s" % (r, slot)] = self.buffer("emb_" + k, torch.float32)[: n * c.emb_dim].view(n, c.emb_dim)
+            out["wide_weights/part_%d/%s" % (r, slot)] = self.buffer("wide_" + k, torch.float32)[:n]
+            out["dense_flat/part_%d/%s" % (r, slot)] = self.buffer("dense_" + k, torch.float32)
+        return out
+
+    def load_shards(self, tensors: Dict[str, "np.ndarray"], step: Optional[int] = None) -> None:
+        """Inverse of :meth:`named_shards` (restore): copies host arrays into the shard, refreshes the
+        bf16 working copies and re-broadcasts this rank's dense range to its peers."""
+        with torch.cuda.device(self.device):
+            for name, dst in self.named_shards().items():
+                if name not in tensors:
+                    raise KeyError("checkpoint has no tensor %r (was it written with world=%d?)" % (name, self.world))
+                src = torch.from_numpy(np.ascontiguousarray(tensors[name])).to(self.device)
+                dst.copy_(src.view_as(dst))
+            _lib.check(self._L.dtf_wd_refresh_embedding(self._h, self._stream()), "dtf_wd_refresh_embedding")
+            _lib.check(self._L.dtf_wd_broadcast_dense(self._h, self._stream()), "dtf_wd_broadcast_dense")
+            torch.cuda.synchronize(self.device)
+        if step is not None:
+            self.step_offset = int(step) - self.global_step()
+
+    step_offset = 0
+
+    def export_config(self) -> dict:
+        d = asdict(self.cfg)
+        d["world"] = self.world
+        return d
 
     def profile(self, on: bool) -> None:
         """Per-kernel tracing: CUDA events between the launches of every executor call."""

@@ -1,0 +1,127 @@
+"""Predictor for exported wide-and-deep models (the serving-batch forward).
+
+On a GPU the exported shards are loaded into a single-rank plan and requests run the same fused
+kernels as training (embedding gather + tcgen05 GEMM chain + logit kernel) with the request's batch
+size; without a GPU a NumPy restatement serves (slow, for tests and tooling).  Serves the
+``{keys, features}`` endpoint of the reference README (README.md:37-41): ``features`` holds, per
+example, the F sparse ids followed by the dense features.
+"""
+from __future__ import annotations
+
+from typing import Dict
+
+import numpy as np
+
+
+def assemble(variables: Dict[str, np.ndarray], name: str, world: int) -> np.ndarray:
+    """Undo ``row r -> part_(r % world)[r // world]`` / range sharding."""
+    parts = [variables["%s/part_%d" % (name, r)] for r in range(world)]
+    if name == "dense_flat":
+        return np.concatenate(parts)
+    rows = sum(p.shape[0] for p in parts)
+    out = np.empty((rows,) + parts[0].shape[1:], dtype=parts[0].dtype)
+    for r, p in enumerate(parts):
+        out[r::world] = p
+    return out
+
+
+class WideDeepPredictor:
+    def __init__(self, variables: Dict[str, np.ndarray], config: dict, device: str = "auto", max_batch: int = 4096):
+        self.config = dict(config)
+        world = int(config.get("world", 1))
+        self.slots, self.dense_in = int(config["slots"]), int(config["dense_in"])
+        emb = assemble(variables, "embedding", world)
+        wide = assemble(variables, "wide_weights", world)
+        flat = assemble(variables, "dense_flat", world)
+        use_gpu = device in ("auto", "cuda")
+        if use_gpu:
+            try:
+                import torch
+                use_gpu = torch.cuda.is_available()
+            except Exception:  # noqa: BLE001
+                use_gpu = False
+        if device == "cuda" and not use_gpu:
+            raise RuntimeError("device=cuda requested but no GPU is visible")
+        self.max_batch = max_batch
+        if use_gpu:
+            self._init_gpu(emb, wide, flat)
+        else:
+            self._init_cpu(emb, wide, flat)
+
+    # ------------------------------------------------------------------ GPU
+    def _init_gpu(self, emb, wide, flat):
+        import torch
+        from .wide_deep import WideDeepConfig, WideDeepTrainer
+        c = self.config
+        cfg = WideDeepConfig(emb_rows=int(c["emb_rows"]), emb_dim=int(c["emb_dim"]), slots=self.slots, dense_in=self.dense_in,
+                             dense_pad=int(c["dense_pad"]), h1=int(c["h1"]), h2=int(c["h2"]), h3=int(c["h3"]),
+                             batch=self.max_batch, optimizer="sgd", sync=False)
+        self._torch = torch
+        self._tr = WideDeepTrainer(cfg)
+        n = self._tr.info.dense_hi - self._tr.info.dense_lo
+        dense = np.zeros(n, np.float32)
+        dense[: min(n, flat.size)] = flat[:n]
+        self._tr.load_shards({"embedding/part_0": emb, "wide_weights/part_0": wide, "dense_flat/part_0": dense})
+        dev = self._tr.device
+        self._ids = torch.zeros(self.max_batch, self.slots, dtype=torch.int32, device=dev)
+        self._dense = torch.zeros(self.max_batch, self.dense_in, dtype=torch.float32, device=dev)
+        self._h_ids = torch.zeros(self.max_batch, self.slots, dtype=torch.int32).pin_memory()
+        self._h_dense = torch.zeros(self.max_batch, self.dense_in, dtype=torch.float32).pin_memory()
+        self._h_out = torch.zeros(self.max_batch, dtype=torch.float32).pin_memory()
+        self.backend = "cuda"
+
+    def _predict_gpu(self, ids: np.ndarray, dense: np.ndarray) -> np.ndarray:
+        torch = self._torch
+        out = np.empty(ids.shape[0], np.float32)
+        for lo in range(0, ids.shape[0], self.max_batch):
+            n = min(self.max_batch, ids.shape[0] - lo)
+            self._h_ids[:n].copy_(torch.from_numpy(ids[lo:lo + n]))
+            self._h_dense[:n].copy_(torch.from_numpy(dense[lo:lo + n]))
+            self._ids[:n].copy_(self._h_ids[:n], non_blocking=True)
+            self._dense[:n].copy_(self._h_dense[:n], non_blocking=True)
+            p = self._tr.predict(self._ids, self._dense, n=n)
+            self._h_out[:n].copy_(p, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            out[lo:lo + n] = self._h_out[:n].numpy()
+        return out
+
+    # ------------------------------------------------------------------ CPU
+    def _init_cpu(self, emb, wide, flat):
+        c = self.config
+        K0 = self.slots * int(c["emb_dim"]) + int(c["dense_pad"])
+        h1, h2, h3 = int(c["h1"]), int(c["h2"]), int(c["h3"])
+        al = lambda v: (v + 255) // 256 * 256
+        o = 0
+        self.w1 = flat[o:o + h1 * K0].reshape(h1, K0); o = al(o + h1 * K0)
+        self.w2 = flat[o:o + h2 * h1].reshape(h2, h1); o = al(o + h2 * h1)
+        self.w3 = flat[o:o + h3 * h2].reshape(h3, h2); o = al(o + h3 * h2)
+        self.b1 = flat[o:o + h1]; o = al(o + h1)
+        self.b2 = flat[o:o + h2]; o = al(o + h2)
+        self.b3 = flat[o:o + h3]; o = al(o + h3)
+        self.w4 = flat[o:o + h3]; o = al(o + h3)
+        self.b4 = flat[o]; self.wide_b = flat[o + 4]
+        self.emb, self.wide = emb, wide
+        self.backend = "numpy"
+
+    def _predict_cpu(self, ids: np.ndarray, dense: np.ndarray) -> np.ndarray:
+        c = self.config
+        B = ids.shape[0]
+        x = np.zeros((B, int(c["dense_pad"])), np.float32)
+        x[:, : self.dense_in] = dense
+        a = np.concatenate([self.emb[ids].reshape(B, -1), x], axis=1)
+        h = np.maximum(a @ self.w1.T + self.b1, 0)
+        h = np.maximum(h @ self.w2.T + self.b2, 0)
+        h = np.maximum(h @ self.w3.T + self.b3, 0)
+        logit = h @ self.w4 + self.b4 + self.wide[ids].sum(1) + self.wide_b
+        return (1.0 / (1.0 + np.exp(-logit))).astype(np.float32)
+
+    # ------------------------------------------------------------------ endpoint
+    def predict(self, inputs: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
+        keys = np.asarray(inputs["keys"]).astype(np.int32)
+        feats = np.asarray(inputs["features"], np.float32)
+        if feats.ndim != 2 or feats.shape[1] != self.slots + self.dense_in:
+            raise ValueError("features must be [batch, %d] (ids then dense values)" % (self.slots + self.dense_in))
+        ids = np.ascontiguousarray(feats[:, : self.slots].astype(np.int32))
+        dense = np.ascontiguousarray(feats[:, self.slots:])
+        p = self._predict_gpu(ids, dense) if self.backend == "cuda" else self._predict_cpu(ids, dense)
+        return {"keys": keys, "prediction": p.reshape(-1, 1)}

@@ -145,7 +145,7 @@ int dtf_wd_step_compute(dtf_wd_plan*, const int* ids, const float* dense, const 
 int dtf_wd_barrier(dtf_wd_plan*, int publish_counts, void* stream);
 int dtf_wd_step_apply(dtf_wd_plan*, void* stream);
 int dtf_wd_step(dtf_wd_plan*, const int* ids, const float* dense, const float* labels, void* stream);
-int dtf_wd_predict(dtf_wd_plan*, const int* ids, const float* dense, void* stream);
+int dtf_wd_predict(dtf_wd_plan*, const int* ids, const float* dense, int n /* <= batch */, void* stream);
 int dtf_wd_read_loss(dtf_wd_plan*, float* loss_sum, void* stream);
 void* dtf_wd_loss_ptr(dtf_wd_plan*);
 /* per-kernel tracing with CUDA events (the reference only prints wall-clock, trainer/task.py:100-102) */

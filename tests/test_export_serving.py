@@ -105,3 +105,32 @@ def test_load_saved_model_roundtrip(tmp_path):
     m = load_saved_model(os.path.join(base, "1"))
     assert float(m["variables"]["weight"]) == 2.0 and m["description"]["model"] == "linear"
     assert m["description"]["signature"]["outputs"]["prediction"]["name"] == "add:0"
+
+
+def test_wide_deep_numpy_predictor_assembles_shards_and_serves():
+    """CPU restatement of the serving forward on synthetic shards from two ranks."""
+    from distributed_tensorflow_b200.models.wide_deep_serving import WideDeepPredictor, assemble
+    rng = np.random.RandomState(0)
+    cfg = dict(emb_rows=11, emb_dim=128, slots=2, dense_in=3, dense_pad=64, h1=64, h2=64, h3=256, world=2)
+    K0 = 2 * 128 + 64
+    al = lambda v: (v + 255) // 256 * 256
+    P = al(al(al(al(al(al(al(64 * K0) + 64 * 64) + 256 * 64) + 64) + 64) + 256) + 256) + 8
+    P_pad = (P + 511) // 512 * 512
+    flat = (rng.randn(P_pad) * 0.05).astype(np.float32)
+    emb = rng.randn(11, 128).astype(np.float32)
+    wide = rng.randn(11).astype(np.float32)
+    variables = {"embedding/part_0": emb[0::2], "embedding/part_1": emb[1::2], "wide_weights/part_0": wide[0::2],
+                 "wide_weights/part_1": wide[1::2], "dense_flat/part_0": flat[: P_pad // 2], "dense_flat/part_1": flat[P_pad // 2:]}
+    assert np.array_equal(assemble(variables, "embedding", 2), emb)
+    p = WideDeepPredictor(variables, cfg, device="cpu")
+    feats = np.array([[3, 10, 0.5, -1.0, 2.0], [0, 0, 0.0, 0.0, 0.0]], np.float32)
+    out = p.predict({"keys": [[7.0], [8.0]], "features": feats})
+    assert out["keys"].tolist() == [[7], [8]] and out["prediction"].shape == (2, 1)
+    assert np.all((out["prediction"] > 0) & (out["prediction"] < 1))
+    x = np.zeros(64, np.float32); x[:3] = feats[0, 2:]
+    a = np.concatenate([emb[3], emb[10], x])
+    h = np.maximum(p.w1 @ a + p.b1, 0); h = np.maximum(p.w2 @ h + p.b2, 0); h = np.maximum(p.w3 @ h + p.b3, 0)
+    logit = h @ p.w4 + p.b4 + wide[3] + wide[10] + p.wide_b
+    assert np.isclose(out["prediction"][0, 0], 1 / (1 + np.exp(-logit)), rtol=1e-4)
+    with pytest.raises(ValueError):
+        p.predict({"keys": [[1]], "features": [[1.0, 2.0]]})
