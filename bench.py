@@ -131,10 +131,7 @@ def main() -> int:
                          lr=0.05)
     tr = WideDeepTrainer(cfg, rank=rank, world=world, device=dev)
     if world > 1:
-        handles = [None] * world
-        dist.all_gather_object(handles, tr.slab_handle())
-        tr.attach_ipc(handles)
-        host_barrier()
+        tr.attach_peers(dist)
     tr.init_params()
     torch.cuda.synchronize()
     host_barrier()
@@ -183,9 +180,14 @@ def main() -> int:
         tr.step(s_ids, s_dense, s_labels)          # count the launches of one step outside the graph
         launches_per_step = _lib.launch_count()
         stream.synchronize()
-        host_barrier()
+        # Start the clock sampler BEFORE the barrier (spawning nvidia-smi takes tens of ms; doing it
+        # after the barrier on rank 0 only would make every other rank's timed region wait for it),
+        # then align the GPUs with one untimed step -- its device-side barriers bring all streams to
+        # the same point within microseconds -- and only then record the start event.
         sampler = ClockSampler(local_rank) if rank == 0 else None
         torch.cuda.synchronize()
+        host_barrier()
+        one_step()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for i in range(args.steps):
@@ -197,7 +199,8 @@ def main() -> int:
         dev_ms = e0.elapsed_time(e1)
         # ---------------- end-to-end region: pinned host -> device every step, loss read back -----
         host_barrier()
-        torch.cuda.synchronize()
+        one_step()
+        stream.synchronize()
         t0 = time.perf_counter()
         e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e2.record(stream)

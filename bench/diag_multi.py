@@ -20,10 +20,7 @@ if world > 1:
 cfg = WideDeepConfig(sync=(mode == "sync"))
 tr = WideDeepTrainer(cfg, rank=rank, world=world, device=dev)
 if world > 1:
-    hs = [None] * world
-    dist.all_gather_object(hs, tr.slab_handle())
-    tr.attach_ipc(hs)
-    dist.barrier()
+    tr.attach_peers(dist)
 tr.init_params()
 torch.cuda.synchronize()
 if world > 1:

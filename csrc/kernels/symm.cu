@@ -1,30 +1,233 @@
-// Symmetric heap: one cudaMalloc'd slab per rank whose CUDA-IPC handle is exchanged over the host
-// control plane and mapped by every peer, so that device code can address any rank's parameter
-// shard, mailbox or signal pad with plain loads/stores over NVLink 5 / NVSwitch.
+// Symmetric heap: one slab of device memory per rank that every peer maps, so that device code can
+// address any rank's parameter shard, mailbox or signal pad with plain loads/stores over NVLink 5 /
+// NVSwitch.  This is the data plane that replaces the gRPC RecvTensor traffic behind every sess.run
+// of the reference (reference trainer/task.py:236); the host side only passes one
+// file descriptor per rank at start-up.
 //
-// This is the data plane that replaces the gRPC RecvTensor traffic behind every sess.run of the
-// reference (reference trainer/task.py:236).  The host side only exchanges 64-byte
-// handles once at start-up.
+// Slabs are created with the virtual-memory-management API (cuMemCreate, 2 MB granularity) and
+// shared as POSIX file descriptors.  Measured on 2 x B200: a peer mapping made by
+// cudaIpcOpenMemHandle serves the fused pull's 256-byte row reads 3x slower than a VMM / direct
+// peer mapping (486 us vs 165 us for 54 MB), so the legacy IPC handle path is kept only as a
+// fallback for drivers that cannot export file descriptors.
+#include <unistd.h>
+
+#include <map>
+#include <mutex>
+
 #include "../../include/dtf_kernels.h"
 #include "common.cuh"
 
 using namespace dtf;
 
+namespace {
+
+struct Drv {
+  CUresult (*GetGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags) = nullptr;
+  CUresult (*Create)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long) = nullptr;
+  CUresult (*Release)(CUmemGenericAllocationHandle) = nullptr;
+  CUresult (*AddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+  CUresult (*AddressFree)(CUdeviceptr, size_t) = nullptr;
+  CUresult (*Map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+  CUresult (*Unmap)(CUdeviceptr, size_t) = nullptr;
+  CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
+  CUresult (*Export)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long) = nullptr;
+  CUresult (*Import)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType) = nullptr;
+  bool ok = false;
+};
+
+template <typename T>
+bool load(const char* name, T* fn) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  *fn = reinterpret_cast<T>(p);
+  return true;
+}
+
+Drv& drv() {
+  static Drv d;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    d.ok = load("cuMemGetAllocationGranularity", &d.GetGranularity) && load("cuMemCreate", &d.Create) &&
+           load("cuMemRelease", &d.Release) && load("cuMemAddressReserve", &d.AddressReserve) &&
+           load("cuMemAddressFree", &d.AddressFree) && load("cuMemMap", &d.Map) && load("cuMemUnmap", &d.Unmap) &&
+           load("cuMemSetAccess", &d.SetAccess) && load("cuMemExportToShareableHandle", &d.Export) &&
+           load("cuMemImportFromShareableHandle", &d.Import);
+  });
+  return d;
+}
+
+struct Mapping {
+  CUmemGenericAllocationHandle handle = 0;
+  size_t size = 0;   // rounded to the granularity
+  bool vmm = false;  // false: legacy cudaMalloc allocation
+  bool imported = false;
+};
+std::mutex g_mu;
+std::map<void*, Mapping> g_maps;
+
+int map_handle(CUmemGenericAllocationHandle h, size_t size, int dev, void** out) {
+  Drv& d = drv();
+  CUdeviceptr va = 0;
+  CUresult r = d.AddressReserve(&va, size, 0, 0, 0);
+  if (r != CUDA_SUCCESS) {
+    set_error("symm: cuMemAddressReserve(%zu) failed (%d)", size, (int)r);
+    return -1;
+  }
+  r = d.Map(va, size, 0, h, 0);
+  if (r != CUDA_SUCCESS) {
+    d.AddressFree(va, size);
+    set_error("symm: cuMemMap failed (%d)", (int)r);
+    return -1;
+  }
+  CUmemAccessDesc acc{};
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = dev;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  r = d.SetAccess(va, size, &acc, 1);
+  if (r != CUDA_SUCCESS) {
+    d.Unmap(va, size);
+    d.AddressFree(va, size);
+    set_error("symm: cuMemSetAccess for device %d failed (%d) -- no peer access between the GPUs?", dev, (int)r);
+    return -1;
+  }
+  *out = reinterpret_cast<void*>(va);
+  return 0;
+}
+
+}  // namespace
+
 extern "C" {
 
 int dtf_symm_alloc(size_t bytes, void** out_ptr) {
+  int dev = 0;
+  DTF_CUDA_OK(cudaGetDevice(&dev));
+  DTF_CUDA_OK(cudaFree(nullptr));  // make sure the primary context exists before driver calls
+  Drv& d = drv();
+  if (d.ok) {
+    CUmemAllocationProp prop{};
+    prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    prop.location.id = dev;
+    prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t gran = 0;
+    if (d.GetGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) == CUDA_SUCCESS && gran > 0) {
+      const size_t size = (bytes + gran - 1) / gran * gran;
+      CUmemGenericAllocationHandle h = 0;
+      const CUresult r = d.Create(&h, size, &prop, 0);
+      if (r == CUDA_SUCCESS) {
+        void* p = nullptr;
+        if (map_handle(h, size, dev, &p) != 0) {
+          d.Release(h);
+          return -1;
+        }
+        DTF_CUDA_OK(cudaMemset(p, 0, size));
+        std::lock_guard<std::mutex> l(g_mu);
+        g_maps[p] = Mapping{h, size, true, false};
+        *out_ptr = p;
+        return 0;
+      }
+    }
+  }
+  // fallback: plain cudaMalloc (shareable through the legacy IPC handle only)
   void* p = nullptr;
   DTF_CUDA_OK(cudaMalloc(&p, bytes));
   DTF_CUDA_OK(cudaMemset(p, 0, bytes));
+  std::lock_guard<std::mutex> l(g_mu);
+  g_maps[p] = Mapping{0, bytes, false, false};
   *out_ptr = p;
   return 0;
 }
 
 int dtf_symm_free(void* ptr) {
-  DTF_CUDA_OK(cudaFree(ptr));
+  Mapping m;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    auto it = g_maps.find(ptr);
+    if (it == g_maps.end()) {
+      set_error("symm: %p was not allocated by dtf_symm_alloc / imported", ptr);
+      return -2;
+    }
+    m = it->second;
+    g_maps.erase(it);
+  }
+  if (!m.vmm) {
+    DTF_CUDA_OK(cudaFree(ptr));
+    return 0;
+  }
+  Drv& d = drv();
+  d.Unmap(reinterpret_cast<CUdeviceptr>(ptr), m.size);
+  d.AddressFree(reinterpret_cast<CUdeviceptr>(ptr), m.size);
+  d.Release(m.handle);
   return 0;
 }
 
+// 1 when slabs are VMM allocations that can be shared as file descriptors
+int dtf_symm_is_vmm(void* ptr) {
+  std::lock_guard<std::mutex> l(g_mu);
+  auto it = g_maps.find(ptr);
+  return it != g_maps.end() && it->second.vmm ? 1 : 0;
+}
+
+long long dtf_symm_mapped_size(void* ptr) {
+  std::lock_guard<std::mutex> l(g_mu);
+  auto it = g_maps.find(ptr);
+  return it == g_maps.end() ? -1 : static_cast<long long>(it->second.size);
+}
+
+// POSIX file descriptor of a VMM slab (caller closes it after it has been sent to the peers)
+int dtf_symm_export_fd(void* ptr, int* fd_out) {
+  Mapping m;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    auto it = g_maps.find(ptr);
+    if (it == g_maps.end() || !it->second.vmm) {
+      set_error("symm: %p is not a VMM allocation", ptr);
+      return -2;
+    }
+    m = it->second;
+  }
+  int fd = -1;
+  const CUresult r = drv().Export(&fd, m.handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+  if (r != CUDA_SUCCESS) {
+    set_error("symm: cuMemExportToShareableHandle failed (%d)", (int)r);
+    return -1;
+  }
+  *fd_out = fd;
+  return 0;
+}
+
+// map a peer's slab received as a file descriptor; `size` is dtf_symm_mapped_size() on the owner
+int dtf_symm_import_fd(int fd, size_t size, void** out_ptr) {
+  int dev = 0;
+  DTF_CUDA_OK(cudaGetDevice(&dev));
+  DTF_CUDA_OK(cudaFree(nullptr));
+  Drv& d = drv();
+  if (!d.ok) {
+    set_error("symm: VMM driver entry points unavailable");
+    return -1;
+  }
+  CUmemGenericAllocationHandle h = 0;
+  const CUresult r = d.Import(&h, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+  if (r != CUDA_SUCCESS) {
+    set_error("symm: cuMemImportFromShareableHandle failed (%d)", (int)r);
+    return -1;
+  }
+  void* p = nullptr;
+  if (map_handle(h, size, dev, &p) != 0) {
+    d.Release(h);
+    return -1;
+  }
+  std::lock_guard<std::mutex> l(g_mu);
+  g_maps[p] = Mapping{h, size, true, true};
+  *out_ptr = p;
+  return 0;
+}
+
+// ---- legacy CUDA IPC handles (fallback) -------------------------------------------------------
 int dtf_symm_handle_size(void) { return static_cast<int>(sizeof(cudaIpcMemHandle_t)); }
 
 int dtf_symm_get_handle(void* ptr, void* handle_out) {
@@ -44,12 +247,19 @@ int dtf_symm_open_handle(const void* handle, void** out_ptr) {
 }
 
 int dtf_symm_close_handle(void* ptr) {
-  DTF_CUDA_OK(cudaIpcCloseMemHandle(ptr));
-  return 0;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    if (g_maps.count(ptr)) {
+      // imported VMM mapping
+    } else {
+      DTF_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+      return 0;
+    }
+  }
+  return dtf_symm_free(ptr);
 }
 
-// Same-process peers (several "ranks" driven from one process, e.g. tests on one box with several
-// GPUs): enable direct peer access instead of IPC.
+// Same-process peers (several ranks driven from one process): enable direct peer access.
 int dtf_symm_enable_peer(int peer_device) {
   int dev = 0;
   DTF_CUDA_OK(cudaGetDevice(&dev));

@@ -85,6 +85,24 @@ struct dtf_wd_plan {
   }
 };
 
+// zero fill by kernel instead of cudaMemsetAsync: memset nodes on IPC-exported (peer-mapped) memory
+// made CUDA-graph replays of the multi-rank step slow
+__global__ void wd_zero_kernel(uint4* __restrict__ p, size_t n16) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n16;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    p[i] = make_uint4(0, 0, 0, 0);
+}
+static int zero_fill(void* ptr, size_t bytes, cudaStream_t st) {
+  const size_t n16 = (bytes + 15) / 16;
+  int grid = static_cast<int>((n16 + 255) / 256);
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  if (grid < 1) grid = 1;
+  wd_zero_kernel<<<grid, 256, 0, st>>>(static_cast<uint4*>(ptr), n16);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
 static void mark(dtf_wd_plan* p, cudaStream_t st, const char* name) {
   if (!p->profile) return;
   cudaEvent_t e;
@@ -222,8 +240,8 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   ok &= (p->dlogit = p->alloc<float>("dlogit", B)) != nullptr;
   ok &= (p->prob = p->alloc<float>("prob", B)) != nullptr;
   const int m_tiles = (sh.B + BM - 1) / BM;
-  p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles) * 4;
-  ok &= (p->zero_region = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles)) != nullptr;
+  p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles) * 4;   // the allocation below is padded to 16-byte multiples
+  ok &= (p->zero_region = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles + 8)) != nullptr;
   ok &= (p->state = p->alloc<StepState>("step_state", 1)) != nullptr;
   if (!ok) {
     dtf_wd_destroy(p);
@@ -239,9 +257,9 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
 void dtf_wd_destroy(dtf_wd_plan* p) {
   if (!p) return;
   cudaDeviceSynchronize();
-  for (void* m : p->opened) cudaIpcCloseMemHandle(m);
+  for (void* m : p->opened) dtf_symm_close_handle(m);
   for (void* q : p->owned) cudaFree(q);
-  if (p->slab && p->owns_slab) cudaFree(p->slab);
+  if (p->slab && p->owns_slab) dtf_symm_free(p->slab);
   (void)cudaGetLastError();
   delete p;
 }
@@ -289,6 +307,21 @@ int dtf_wd_attach_ipc(dtf_wd_plan* p, const void* handles) {
   }
   return 0;
 }
+
+// peers' slabs received as POSIX file descriptors (VMM allocations, 2 MB pages); own entry ignored
+int dtf_wd_attach_fds(dtf_wd_plan* p, const int* fds) {
+  const long long size = dtf_symm_mapped_size(p->slab);
+  for (int r = 0; r < p->cfg.world; ++r) {
+    if (r == p->cfg.rank) continue;
+    void* m = nullptr;
+    if (dtf_symm_import_fd(fds[r], static_cast<size_t>(size), &m) != 0) return -1;
+    p->opened.push_back(m);
+    p->pt.slab[r] = static_cast<uint8_t*>(m);
+  }
+  return 0;
+}
+int dtf_wd_slab_fd(dtf_wd_plan* p, int* fd_out) { return dtf_symm_export_fd(p->slab, fd_out); }
+int dtf_wd_slab_is_vmm(dtf_wd_plan* p) { return dtf_symm_is_vmm(p->slab); }
 
 // same-process peers: raw slab pointers of the other plans (tests, single-process multi-GPU)
 int dtf_wd_attach_ptrs(dtf_wd_plan* p, void* const* slabs) {
@@ -351,7 +384,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   const DenseLayout& dl = p->dl;
   const int n = sh.B * sh.F;
   mark(p, st, "begin");
-  DTF_CUDA_OK(cudaMemsetAsync(p->zero_region, 0, p->zero_bytes, st));
+  if (zero_fill(p->zero_region, p->zero_bytes, st) != 0) return -1;
   wd_route_kernel<<<(n + 255) / 256, 256, 0, st>>>(ids, n, sh.V, p->pt, p->sl, sh.cap, p->cnt, p->row_src, p->wide_src,
                                                    p->row_dst, p->dl_dst);
   wd_dense_pad_kernel<<<(sh.B * sh.dense_pad + 255) / 256, 256, 0, st>>>(dense_raw, p->dense_x, sh.B, sh.dense_in,
@@ -525,7 +558,7 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   mark(p, st, "step");
-  DTF_CUDA_OK(cudaMemsetAsync(p->slab + p->sl.dense_grad, 0, static_cast<size_t>(p->P_pad) * 4, st));
+  if (zero_fill(p->slab + p->sl.dense_grad, static_cast<size_t>(p->P_pad) * 4, st) != 0) return -1;
   if (forward(p, ids, dense_raw, st, true) != 0) return -1;
   if (launch_loss(p, labels, st, true) != 0) return -1;
   mark(p, st, "loss+wide");

@@ -150,6 +150,35 @@ class WideDeepTrainer:
             _lib.check(self._L.dtf_wd_attach_ipc(self._h, blob), "dtf_wd_attach_ipc")
         self._attached = True
 
+    def attach_peers(self, dist_module=None) -> None:
+        """Map every peer's slab (collective over the default process group).  Slabs are VMM
+        allocations shared as file descriptors over Unix sockets; CUDA-IPC handles are only the
+        fallback (their mappings serve fine-grained remote reads about 3x slower)."""
+        from ..parallel import symm
+        if self.world == 1:
+            return
+        self._L.dtf_wd_slab_is_vmm.argtypes = [C.c_void_p]
+        self._L.dtf_wd_slab_fd.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        self._L.dtf_wd_attach_fds.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        import torch.distributed as dist
+        d = dist_module or dist
+        flags = [None] * self.world
+        d.all_gather_object(flags, bool(self._L.dtf_wd_slab_is_vmm(self._h)))
+        if all(flags):
+            fd = C.c_int(-1)
+            _lib.check(self._L.dtf_wd_slab_fd(self._h, C.byref(fd)), "dtf_wd_slab_fd")
+            fds = symm.exchange_fds(fd.value, self.rank, self.world, d)
+            arr = (C.c_int * self.world)(*[f if f is not None else -1 for f in fds])
+            with torch.cuda.device(self.device):
+                _lib.check(self._L.dtf_wd_attach_fds(self._h, arr), "dtf_wd_attach_fds")
+            symm.close_fds([fd.value] + [f for f in fds if f is not None])
+            self._attached = True
+        else:
+            handles = [None] * self.world
+            d.all_gather_object(handles, self.slab_handle())
+            self.attach_ipc(handles)
+        d.barrier()
+
     def attach_local(self, peers: List["WideDeepTrainer"]) -> None:
         """Peers living in this process (several ranks emulated on one device, or one process
         driving several GPUs)."""

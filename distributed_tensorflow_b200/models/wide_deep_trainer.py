@@ -61,8 +61,7 @@ def make_trainer(cfg: WideDeepConfig, d: _Dist) -> WideDeepTrainer:
     torch.cuda.set_device(d.local_rank)
     tr = WideDeepTrainer(cfg, rank=d.rank, world=d.world, device=torch.device("cuda", d.local_rank))
     if d.world > 1:
-        tr.attach_ipc(d.all_gather_object(tr.slab_handle()))
-        d.barrier()
+        tr.attach_peers(d.pg)
     return tr
 
 

@@ -89,8 +89,12 @@ int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, const void* de
 /* ---- symmetric heap (peer-mapped HBM over NVLink / NVSwitch) --------------------------------- *
  * Data plane that replaces the gRPC Send/Recv traffic of every sess.run in the reference
  * (trainer/task.py:236).  Handles are opaque byte strings exchanged by the host control plane. */
-int dtf_symm_alloc(size_t bytes, void** out_ptr);             /* zero-filled */
+int dtf_symm_alloc(size_t bytes, void** out_ptr);             /* zero-filled; VMM allocation when possible */
 int dtf_symm_free(void* ptr);
+int dtf_symm_is_vmm(void* ptr);                               /* 1: shareable as a file descriptor */
+long long dtf_symm_mapped_size(void* ptr);
+int dtf_symm_export_fd(void* ptr, int* fd_out);               /* POSIX fd of a VMM slab */
+int dtf_symm_import_fd(int fd, size_t size, void** out_ptr);  /* maps a peer's slab (2 MB pages) */
 int dtf_symm_handle_size(void);
 int dtf_symm_get_handle(void* ptr, void* handle_out);
 int dtf_symm_open_handle(const void* handle, void** out_ptr); /* maps a peer's slab */
@@ -136,7 +140,10 @@ int dtf_wd_info(dtf_wd_plan*, dtf_wd_info_t* out);
 int dtf_wd_buffer(dtf_wd_plan*, const char* name, void** ptr, size_t* bytes);
 int dtf_wd_slab_handle(dtf_wd_plan*, void* handle_out);
 void* dtf_wd_slab_ptr(dtf_wd_plan*);
-int dtf_wd_attach_ipc(dtf_wd_plan*, const void* handles /* world * handle_size bytes */);
+int dtf_wd_slab_is_vmm(dtf_wd_plan*);
+int dtf_wd_slab_fd(dtf_wd_plan*, int* fd_out);
+int dtf_wd_attach_fds(dtf_wd_plan*, const int* fds /* world descriptors, own entry ignored */);
+int dtf_wd_attach_ipc(dtf_wd_plan*, const void* handles /* world * handle_size bytes; legacy, slow mappings */);
 int dtf_wd_attach_ptrs(dtf_wd_plan*, void* const* slabs /* world pointers */);
 int dtf_wd_init_params(dtf_wd_plan*, unsigned long long seed, void* stream);
 int dtf_wd_broadcast_dense(dtf_wd_plan*, void* stream);
