@@ -315,9 +315,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int j = 0; j < 32; ++j) w[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
         }
-        // the staging row must have been read out by the previous chunk's bulk operation
+        // the staging rows must have been read out by the previous chunk's store
         if constexpr (kPush) {
-          tma_store_wait_read<0>();
+          __syncwarp();
         } else {
           if (lane == 0) tma_store_wait_read<0>();
           __syncwarp();
@@ -327,13 +327,25 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const uint32_t a = kPush ? (my_row_smem + j * 16) : (my_row_smem + ((j ^ (lane & 7)) << 4));
           st_shared_v4(a, w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
         }
-        fence_proxy_async_smem();
         if constexpr (kPush) {
+          // Scatter to the owners' mailboxes with full 128-byte segments per row: eight lanes cover
+          // one row's half (8 x 16 B), so every store instruction writes four rows and each row
+          // half leaves the SM -- and crosses NVLink -- as one 128-byte transaction.
+          __syncwarp();
           const int col = n0 + c * 64;
-          const unsigned long long d = pdst[(c * 64) >> 7];
-          if (d != 0ull) bulk_store_1d(reinterpret_cast<uint8_t*>(d) + (col & 127) * 2, my_row_smem, 128);
-          tma_store_commit();
+          const unsigned long long mine = pdst[(c * 64) >> 7];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int r = 4 * u + (lane >> 3);
+            const unsigned long long d = __shfl_sync(0xffffffffu, mine, r);
+            uint32_t x0, x1, x2, x3;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3)
+                         : "r"(stg + r * kPitch + (lane & 7) * 16));
+            if (d != 0ull)
+              st_global_v4(reinterpret_cast<uint8_t*>(d) + (col & 127) * 2 + (lane & 7) * 16, x0, x1, x2, x3);
+          }
         } else {
+          fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
             if constexpr (EPI == EPI_F32_ATOMIC) tma_reduce_add_2d(&tmD, stg, n0 + c * CW, row0);

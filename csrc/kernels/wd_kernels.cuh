@@ -520,27 +520,45 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
 // every peer's working copy (all-gather), all in one pass.  SURVEY.md 2E row K2.
 template <int OPT>
 __global__ void __launch_bounds__(256)
-wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, int src_begin, int src_end,
+wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, int sum_first,
                       float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2,
                       const StepState* __restrict__ stp, long long small_begin) {
+  // sum_first = 1 (sync-replica): one optimizer step on the sum of all replicas' gradients.
+  // sum_first = 0 (async / Hogwild): every replica's gradient is applied on its own, in rank order,
+  //   exactly as if each had been sent separately; all of them are read up front so that the
+  //   NVLink loads overlap.
   const OptConst oc = stp->oc;
   const long long n4 = (hi - lo) >> 2;
   for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < n4;
        q += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long i = lo + q * 4;
-    float4 g = make_float4(0, 0, 0, 0);
-    for (int r = src_begin; r < src_end; ++r) {
-      const float4 t = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
-      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
-    }
+    float4 g[kMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < pt.world) g[r] = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
     float4 w = *reinterpret_cast<float4*>(master + (i - lo));
     float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
     if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + (i - lo));
     if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + (i - lo));
-    opt_update<OPT>(w.x, g.x, a.x, v.x, oc);
-    opt_update<OPT>(w.y, g.y, a.y, v.y, oc);
-    opt_update<OPT>(w.z, g.z, a.z, v.z, oc);
-    opt_update<OPT>(w.w, g.w, a.w, v.w, oc);
+    if (sum_first) {
+      float4 t = make_float4(0, 0, 0, 0);
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < pt.world) { t.x += g[r].x; t.y += g[r].y; t.z += g[r].z; t.w += g[r].w; }
+      opt_update<OPT>(w.x, t.x, a.x, v.x, oc);
+      opt_update<OPT>(w.y, t.y, a.y, v.y, oc);
+      opt_update<OPT>(w.z, t.z, a.z, v.z, oc);
+      opt_update<OPT>(w.w, t.w, a.w, v.w, oc);
+    } else {
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < pt.world) {
+          opt_update<OPT>(w.x, g[r].x, a.x, v.x, oc);
+          opt_update<OPT>(w.y, g[r].y, a.y, v.y, oc);
+          opt_update<OPT>(w.z, g[r].z, a.z, v.z, oc);
+          opt_update<OPT>(w.w, g[r].w, a.w, v.w, oc);
+        }
+    }
     *reinterpret_cast<float4*>(master + (i - lo)) = w;
     if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + (i - lo)) = a;
     if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + (i - lo)) = v;

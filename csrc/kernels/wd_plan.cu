@@ -506,20 +506,10 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
     count_launch();
     mark(p, st, "sparse apply entries");
   }
-  if (p->cfg.sync) {
-    wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, 0, p->cfg.world,
-                                                              p->dense_master, p->dense_s1, p->dense_s2, oc,
-                                                              p->dl.small_begin);
-    count_launch();
-  } else {
-    // Hogwild on the dense shard: each replica's gradient is applied on its own, in rank order
-    for (int r = 0; r < p->cfg.world; ++r) {
-      wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, r, r + 1,
-                                                                p->dense_master, p->dense_s1, p->dense_s2, oc,
-                                                                p->dl.small_begin);
-      count_launch();
-    }
-  }
+  wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
+                                                            p->dense_master, p->dense_s1, p->dense_s2, oc,
+                                                            p->dl.small_begin);
+  count_launch();
   mark(p, st, "dense apply");
   DTF_CUDA_OK(cudaGetLastError());
   return 0;
