@@ -148,7 +148,9 @@ def main() -> int:
     s_ids, s_dense, s_labels = (torch.empty_like(t, device=dev) for t in pool_h[0])   # static graph inputs
     loss_host = torch.zeros(1).pin_memory()
     h2d_bytes = sum(t.numel() * t.element_size() for t in pool_h[0])
-    stream = torch.cuda.Stream(device=dev)
+    # high priority: when the async ps-side apply shares the SMs with the next step's compute, the
+    # compute kernels' CTAs are placed first and the apply fills the remaining room
+    stream = torch.cuda.Stream(device=dev, priority=-1)
 
     def load_static(b):
         s_ids.copy_(b[0], non_blocking=True)
@@ -162,7 +164,10 @@ def main() -> int:
         stream.synchronize()
         host_barrier()
         graph = None
-        if not args.no_graph:
+        # Sync mode replays the whole step as one CUDA graph.  Async mode runs the ps-side applies on
+        # a second stream that overlaps the next step's compute; those cross-step dependencies are
+        # plain stream events, so the step is launched eagerly (the C++ executor keeps that cheap).
+        if not args.no_graph and args.mode == "sync":
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=stream):
                 tr.step(s_ids, s_dense, s_labels)
@@ -193,6 +198,7 @@ def main() -> int:
         for i in range(args.steps):
             load_static(pool_d[i % args.pool])     # device -> device, keeps every step on fresh ids
             one_step()
+        tr.join()                                  # the timed region ends when the last apply has finished
         e1.record(stream)
         stream.synchronize()
         host_barrier()
@@ -211,6 +217,7 @@ def main() -> int:
             loss_host.copy_(tr.last_loss_sum(), non_blocking=True)
             stream.synchronize()                   # the caller looks at every step's loss
             last_loss = float(loss_host[0]) / cfg.batch
+        tr.join()
         e3.record(stream)
         stream.synchronize()
         host_barrier()

@@ -63,6 +63,16 @@ struct dtf_wd_plan {
   std::vector<std::pair<std::string, cudaEvent_t>> marks;
   StepState* state = nullptr;  // device: step counter, barrier epoch, optimizer constants
   long long step = 0;          // host mirror of the number of applies issued
+  // Async mode double-buffers everything a step hands from its compute phase to its apply phase
+  // (mailboxes, dense-gradient buffer, per-step scratch) by step parity, so that the ps-side apply of
+  // step t can run on a second stream while the compute phase of step t+1 is already running.
+  SlabLayout sl_par[2];
+  unsigned int* zero_par[2] = {nullptr, nullptr};
+  long long n_compute = 0, n_apply = 0;
+  cudaEvent_t ev_push[2] = {nullptr, nullptr}, ev_apply[2] = {nullptr, nullptr};
+  bool ev_apply_valid[2] = {false, false};
+  int last_compute_parity = 0;
+  int apply_blocks_per_sm = 8;   // lowered while the apply shares the SMs with the next step's GEMMs
 
   template <typename T>
   T* alloc(const char* name, size_t count) {
@@ -109,6 +119,15 @@ static void mark(dtf_wd_plan* p, cudaStream_t st, const char* name) {
   cudaEventCreate(&e);
   cudaEventRecord(e, st);
   p->marks.emplace_back(name, e);
+}
+
+static void select_parity(dtf_wd_plan* p, int par) {
+  p->sl = p->sl_par[par];
+  p->zero_region = p->zero_par[par];
+  p->cnt = p->zero_region;
+  p->chunk_counter = p->zero_region + kMaxWorld;
+  p->loss_acc = reinterpret_cast<float*>(p->zero_region + kMaxWorld + 4);
+  p->tile_flags = p->zero_region + kMaxWorld + 8;
 }
 
 static int mask_ld(int n) {
@@ -180,7 +199,18 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   sl.mbx_dl = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
   sl.mbx_count = take(kMaxWorld * 4);
   sl.signal = take(kMaxWorld * 64);
+  p->sl_par[0] = sl;
+  p->sl_par[1] = sl;
+  if (!cfg->sync) {
+    SlabLayout& s1 = p->sl_par[1];
+    s1.dense_grad = take(static_cast<size_t>(p->P_pad) * 4);
+    s1.mbx_payload = take(static_cast<size_t>(cfg->world) * sh.cap * kEmbDim * 2);
+    s1.mbx_rows = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
+    s1.mbx_dl = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
+    s1.mbx_count = take(kMaxWorld * 4);
+  }
   sl.total = off;
+  p->sl_par[0].total = p->sl_par[1].total = off;
 
   void* slab = nullptr;
   if (dtf_symm_alloc(sl.total, &slab) != 0) {
@@ -241,22 +271,29 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   ok &= (p->prob = p->alloc<float>("prob", B)) != nullptr;
   const int m_tiles = (sh.B + BM - 1) / BM;
   p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles) * 4;   // the allocation below is padded to 16-byte multiples
-  ok &= (p->zero_region = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles + 8)) != nullptr;
+  ok &= (p->zero_par[0] = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles + 8)) != nullptr;
+  if (cfg->sync) p->zero_par[1] = p->zero_par[0];
+  else ok &= (p->zero_par[1] = p->alloc<unsigned int>("step_scratch1", kMaxWorld + 8 + m_tiles + 8)) != nullptr;
   ok &= (p->state = p->alloc<StepState>("step_state", 1)) != nullptr;
   if (!ok) {
     dtf_wd_destroy(p);
     return nullptr;
   }
-  p->cnt = p->zero_region;
-  p->chunk_counter = p->zero_region + kMaxWorld;
-  p->loss_acc = reinterpret_cast<float*>(p->zero_region + kMaxWorld + 4);
-  p->tile_flags = p->zero_region + kMaxWorld + 8;
+  select_parity(p, 0);
+  for (int i = 0; i < 2; ++i) {
+    cudaEventCreateWithFlags(&p->ev_push[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&p->ev_apply[i], cudaEventDisableTiming);
+  }
   return p;
 }
 
 void dtf_wd_destroy(dtf_wd_plan* p) {
   if (!p) return;
   cudaDeviceSynchronize();
+  for (int i = 0; i < 2; ++i) {
+    if (p->ev_push[i]) cudaEventDestroy(p->ev_push[i]);
+    if (p->ev_apply[i]) cudaEventDestroy(p->ev_apply[i]);
+  }
   for (void* m : p->opened) dtf_symm_close_handle(m);
   for (void* q : p->owned) cudaFree(q);
   if (p->slab && p->owns_slab) dtf_symm_free(p->slab);
@@ -492,7 +529,14 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
   count_launch();
   __nv_bfloat16* work = reinterpret_cast<__nv_bfloat16*>(p->slab + sl.emb_bf16);
   float* wide = reinterpret_cast<float*>(p->slab + sl.wide);
-  const int grid = num_sms() * 8;
+  int grid = num_sms() * 8;
+  if (p->apply_blocks_per_sm != 8) {
+    // overlapped with the next step's compute: many short-lived blocks (one pair of entries per warp)
+    // instead of a persistent grid, so that SMs are handed to the higher-priority GEMM CTAs as soon
+    // as those become runnable and the apply fills whatever room they leave
+    const long long want = (p->sh.cap + 15) / 16;
+    grid = static_cast<int>(want > grid ? want : grid);
+  }
   if (p->cfg.sync) {
     wd_sparse_accum_kernel<<<grid, 256, 0, st>>>(mv, p->G, p->wide_G, p->bitmap);
     mark(p, st, "sparse accum");
@@ -506,7 +550,9 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
     count_launch();
     mark(p, st, "sparse apply entries");
   }
-  wd_dense_apply_kernel<OPT><<<num_sms() * 4, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
+  const long long dense_n4 = (p->dense_hi - p->dense_lo) / 4;
+  const int dense_grid = p->apply_blocks_per_sm != 8 ? static_cast<int>((dense_n4 + 255) / 256) : num_sms() * 4;
+  wd_dense_apply_kernel<OPT><<<dense_grid, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
                                                             p->dense_master, p->dense_s1, p->dense_s2, oc,
                                                             p->dl.small_begin);
   count_launch();
@@ -547,6 +593,10 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
+  const int par = p->cfg.sync ? 0 : static_cast<int>(p->n_compute & 1);
+  select_parity(p, par);
+  p->last_compute_parity = par;
+  p->n_compute += 1;
   mark(p, st, "step");
   if (zero_fill(p->slab + p->sl.dense_grad, static_cast<size_t>(p->P_pad) * 4, st) != 0) return -1;
   if (forward(p, ids, dense_raw, st, true) != 0) return -1;
@@ -581,6 +631,7 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
 // cross-rank barrier on the device (no-op publish for a single rank)
 int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  select_parity(p, p->cfg.sync ? 0 : static_cast<int>(p->n_apply & 1));
   if (p->cfg.world == 1 || p->cfg.no_device_barrier) {
     if (publish_counts) {
       wd_publish_local_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->cnt);
@@ -598,13 +649,17 @@ int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
 // parameter-server side: apply what the mailboxes and gradient buffers hold
 int dtf_wd_step_apply(dtf_wd_plan* p, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  select_parity(p, p->cfg.sync ? 0 : static_cast<int>(p->n_apply & 1));
   int rc;
   switch (p->cfg.optimizer) {
     case WD_SGD: rc = apply_t<WD_SGD>(p, st); break;
     case WD_ADAGRAD: rc = apply_t<WD_ADAGRAD>(p, st); break;
     default: rc = apply_t<WD_ADAM>(p, st); break;
   }
-  if (rc == 0) p->step += 1;
+  if (rc == 0) {
+    p->step += 1;
+    p->n_apply += 1;
+  }
   return rc;
 }
 
@@ -627,6 +682,7 @@ int dtf_wd_predict(dtf_wd_plan* p, const int* ids, const float* dense_raw, int n
   }
   const int full = p->sh.B;
   p->sh.B = n;
+  select_parity(p, p->cfg.sync ? 0 : static_cast<int>(p->n_compute & 1));
   int rc = forward(p, ids, dense_raw, st, false);
   if (rc == 0) rc = launch_loss(p, nullptr, st, false);
   p->sh.B = full;
@@ -641,6 +697,50 @@ int dtf_wd_read_loss(dtf_wd_plan* p, float* loss_sum, void* stream_) {
   return 0;
 }
 
-void* dtf_wd_loss_ptr(dtf_wd_plan* p) { return p->loss_acc; }
+void* dtf_wd_loss_ptr(dtf_wd_plan* p) {
+  return reinterpret_cast<float*>(p->zero_par[p->last_compute_parity] + kMaxWorld + 4);
+}
+int dtf_wd_last_parity(dtf_wd_plan* p) { return p->last_compute_parity; }
+
+// Async (Hogwild) step with the parameter-server side off the critical path: the compute phase of
+// step t runs on `compute_stream`; barrier + apply (+ barrier) of step t run on `apply_stream` and
+// overlap the compute phase of step t+1, which pulls whatever the shards hold at that moment (stale
+// by at most one step, like a TF worker that does not wait for the ps to apply).  Parity-double-
+// buffered mailboxes keep step t+1's pushes away from the entries step t's apply is still reading;
+// a parity's buffers are reused only after the apply that consumed them has finished everywhere.
+int dtf_wd_step_overlapped(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels,
+                           void* compute_stream, void* apply_stream) {
+  if (p->cfg.sync) {
+    set_error("dtf_wd_step_overlapped: sync-replica mode has no apply/compute overlap; use dtf_wd_step");
+    return -2;
+  }
+  cudaStream_t C = reinterpret_cast<cudaStream_t>(compute_stream), A = reinterpret_cast<cudaStream_t>(apply_stream);
+  const int par = static_cast<int>(p->n_compute & 1);
+  if (p->ev_apply_valid[par]) DTF_CUDA_OK(cudaStreamWaitEvent(C, p->ev_apply[par], 0));
+  if (dtf_wd_step_compute(p, ids, dense_raw, labels, compute_stream) != 0) return -1;
+  DTF_CUDA_OK(cudaEventRecord(p->ev_push[par], C));
+  DTF_CUDA_OK(cudaStreamWaitEvent(A, p->ev_push[par], 0));
+  if (dtf_wd_barrier(p, 1, apply_stream) != 0) return -1;
+  // two blocks per SM: the apply must leave thread slots for the next step's persistent GEMM CTAs
+  p->apply_blocks_per_sm = p->cfg.overlap_apply_blocks > 0 ? p->cfg.overlap_apply_blocks : 2;
+  const int arc = dtf_wd_step_apply(p, apply_stream);
+  p->apply_blocks_per_sm = 8;
+  if (arc != 0) return -1;
+  if (p->cfg.world > 1 && dtf_wd_barrier(p, 0, apply_stream) != 0) return -1;
+  DTF_CUDA_OK(cudaEventRecord(p->ev_apply[par], A));
+  p->ev_apply_valid[par] = true;
+  return 0;
+}
+
+// make `stream` wait for every apply issued so far (before reading shards, or to close a capture)
+int dtf_wd_join(dtf_wd_plan* p, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  for (int i = 0; i < 2; ++i)
+    if (p->ev_apply_valid[i]) DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_apply[i], 0));
+  return 0;
+}
+
+// forget cross-step dependencies (call after a full synchronisation, e.g. before capturing a graph)
+void dtf_wd_overlap_reset(dtf_wd_plan* p) { p->ev_apply_valid[0] = p->ev_apply_valid[1] = false; }
 
 }  // extern "C"

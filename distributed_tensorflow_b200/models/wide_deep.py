@@ -20,6 +20,7 @@ reference's ps/worker training loop (/root/reference/trainer/task.py:123-143, 23
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, asdict
 from typing import Dict, List, Optional
 
@@ -57,7 +58,7 @@ class _CConfig(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("batch", C.c_int), ("slots", C.c_int), ("emb_dim", C.c_int),
                 ("dense_in", C.c_int), ("dense_pad", C.c_int), ("h1", C.c_int), ("h2", C.c_int), ("h3", C.c_int),
                 ("emb_rows", C.c_longlong), ("optimizer", C.c_int), ("sync", C.c_int), ("no_device_barrier", C.c_int),
-                ("lr", C.c_float), ("emb_init_scale", C.c_float)]
+                ("lr", C.c_float), ("emb_init_scale", C.c_float), ("overlap_apply_blocks", C.c_int)]
 
 
 class _CInfo(C.Structure):
@@ -103,6 +104,11 @@ def _bind(L):
     L.dtf_wd_read_loss.argtypes = [vp, C.POINTER(C.c_float), vp]
     L.dtf_wd_loss_ptr.restype = vp
     L.dtf_wd_loss_ptr.argtypes = [vp]
+    L.dtf_wd_last_parity.argtypes = [vp]
+    L.dtf_wd_step_overlapped.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.dtf_wd_join.argtypes = [vp, vp]
+    L.dtf_wd_overlap_reset.restype = None
+    L.dtf_wd_overlap_reset.argtypes = [vp]
     L.dtf_symm_handle_size.restype = i
     L._wd_bound = True
 
@@ -123,7 +129,8 @@ class WideDeepTrainer:
         cc = _CConfig(world=world, rank=rank, batch=cfg.batch, slots=cfg.slots, emb_dim=cfg.emb_dim,
                       dense_in=cfg.dense_in, dense_pad=cfg.dense_pad, h1=cfg.h1, h2=cfg.h2, h3=cfg.h3,
                       emb_rows=cfg.emb_rows, optimizer=OPT_IDS[cfg.optimizer], sync=int(cfg.sync),
-                      no_device_barrier=int(no_device_barrier), lr=cfg.lr, emb_init_scale=cfg.emb_init_scale)
+                      no_device_barrier=int(no_device_barrier), lr=cfg.lr, emb_init_scale=cfg.emb_init_scale,
+                      overlap_apply_blocks=int(os.environ.get("DTF_APPLY_BLOCKS", "0")))
         with torch.cuda.device(self.device):
             self._h = self._L.dtf_wd_create(C.byref(cc))
         if not self._h:
@@ -132,7 +139,12 @@ class WideDeepTrainer:
         self._L.dtf_wd_info(self._h, C.byref(self.info))
         self._attached = world == 1
         self._views: Dict[str, torch.Tensor] = {}
-        self.loss_view = self.buffer("step_scratch", torch.float32)[20:21]   # loss_acc lives after cnt + counter
+        # loss accumulators live after cnt[16] + counter[4] in the per-step scratch (one per parity)
+        self._loss_views = [self.buffer("step_scratch", torch.float32)[20:21]]
+        if not cfg.sync:
+            self._loss_views.append(self.buffer("step_scratch1", torch.float32)[20:21])
+        self.loss_view = self._loss_views[0]
+        self._apply_stream: Optional[torch.cuda.Stream] = None
 
     # ------------------------------------------------------------------ set-up
     def slab_handle(self) -> bytes:
@@ -242,10 +254,30 @@ class WideDeepTrainer:
             assert labels.dtype == torch.float32 and labels.numel() == self.cfg.batch
         return C.c_void_p(ids.data_ptr()), C.c_void_p(dense.data_ptr()), C.c_void_p(labels.data_ptr() if labels is not None else 0)
 
-    def step(self, ids: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor) -> None:
-        """One full training step on device-resident inputs (asynchronous)."""
+    def step(self, ids: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor, overlap: Optional[bool] = None) -> None:
+        """One full training step on device-resident inputs (asynchronous on the current stream).
+
+        In async mode (``cfg.sync == False``) the parameter-server side (barrier + applies) runs on an
+        internal second stream and overlaps the next step's compute phase, unless ``overlap=False``."""
         a, b, c = self._ptrs(ids, dense, labels)
-        _lib.check(self._L.dtf_wd_step(self._h, a, b, c, self._stream()), "dtf_wd_step")
+        if overlap is None:
+            overlap = not self.cfg.sync
+        if overlap and not self.cfg.sync:
+            if self._apply_stream is None:
+                self._apply_stream = torch.cuda.Stream(device=self.device)
+            _lib.check(self._L.dtf_wd_step_overlapped(self._h, a, b, c, self._stream(),
+                                                      C.c_void_p(self._apply_stream.cuda_stream)), "dtf_wd_step_overlapped")
+        else:
+            _lib.check(self._L.dtf_wd_step(self._h, a, b, c, self._stream()), "dtf_wd_step")
+
+    def join(self) -> None:
+        """Make the current stream wait for every ps-side apply issued so far (call before reading
+        shards, predicting, checkpointing, or ending a CUDA-graph capture of overlapped steps)."""
+        _lib.check(self._L.dtf_wd_join(self._h, self._stream()), "dtf_wd_join")
+
+    def overlap_reset(self) -> None:
+        """Forget cross-step event dependencies (after a full device synchronisation)."""
+        self._L.dtf_wd_overlap_reset(self._h)
 
     def step_compute(self, ids, dense, labels) -> None:
         a, b, c = self._ptrs(ids, dense, labels)
@@ -261,6 +293,7 @@ class WideDeepTrainer:
         """Probabilities for the first ``n`` examples (default: a full batch).  ``ids`` / ``dense`` may
         hold just ``n`` rows; the result is a view of the plan's ``prob`` buffer."""
         n = int(n if n is not None else ids.shape[0])
+        self.join()
         assert ids.dtype == torch.int32 and ids.is_cuda and ids.is_contiguous() and ids.numel() >= n * self.cfg.slots
         assert dense.dtype == torch.float32 and dense.is_contiguous() and dense.numel() >= n * self.cfg.dense_in
         _lib.check(self._L.dtf_wd_predict(self._h, C.c_void_p(ids.data_ptr()), C.c_void_p(dense.data_ptr()), n,
@@ -271,6 +304,10 @@ class WideDeepTrainer:
     _SLOT_NAMES = {"adagrad": ("Adagrad",), "adam": ("Adam", "Adam_1"), "sgd": ()}
 
     def named_shards(self) -> Dict[str, torch.Tensor]:
+        self.join()
+        return self._named_shards()
+
+    def _named_shards(self) -> Dict[str, torch.Tensor]:
         """This rank's ps shard as named device tensors (fp32 masters + optimizer slots), using the
         ``<variable>/part_<rank>`` convention for partitioned variables and TF slot names."""
         c, r = self.cfg, self.rank
@@ -326,7 +363,7 @@ class WideDeepTrainer:
 
     def last_loss_sum(self) -> torch.Tensor:
         """Device scalar: sum over the micro-batch of the per-example loss of the last step."""
-        return self.loss_view
+        return self._loss_views[int(self._L.dtf_wd_last_parity(self._h)) if not self.cfg.sync else 0]
 
     def global_step(self) -> int:
         self._L.dtf_wd_info(self._h, C.byref(self.info))

@@ -227,6 +227,7 @@ def run_wide_deep(flags) -> None:
     last_save = time.time()
     ckpt.save(step0)                                       # Supervisor: first save right away
     step = step0
+    torch.cuda.set_stream(torch.cuda.Stream(device=tr.device, priority=-1))   # compute outranks the ps-side apply
     for epoch in range(flags.max_epochs):
         for _ in range(steps_per_epoch):
             tr.step(*synthetic_batch(cfg, gen, tr.device))

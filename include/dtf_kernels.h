@@ -122,6 +122,7 @@ typedef struct dtf_wd_config {
   int no_device_barrier; /* 1: caller orders ranks itself (several ranks emulated on one GPU) */
   float lr;
   float emb_init_scale;
+  int overlap_apply_blocks; /* async overlap: apply blocks per SM (0 = default 2) */
 } dtf_wd_config;
 
 typedef struct dtf_wd_info_t {
@@ -154,7 +155,16 @@ int dtf_wd_step_apply(dtf_wd_plan*, void* stream);
 int dtf_wd_step(dtf_wd_plan*, const int* ids, const float* dense, const float* labels, void* stream);
 int dtf_wd_predict(dtf_wd_plan*, const int* ids, const float* dense, int n /* <= batch */, void* stream);
 int dtf_wd_read_loss(dtf_wd_plan*, float* loss_sum, void* stream);
-void* dtf_wd_loss_ptr(dtf_wd_plan*);
+void* dtf_wd_loss_ptr(dtf_wd_plan*);   /* loss accumulator of the most recent compute phase */
+int dtf_wd_last_parity(dtf_wd_plan*);
+/* Async mode only: compute of step t on compute_stream, ps-side barrier + apply of step t on
+ * apply_stream, overlapping the compute of step t+1 (bounded staleness of one step; mailboxes,
+ * gradient buffers and scratch are double-buffered by step parity).  The async counterpart of a TF
+ * worker that does not wait for the ps to apply (reference trainer/task.py:138, no sync wrapper). */
+int dtf_wd_step_overlapped(dtf_wd_plan*, const int* ids, const float* dense, const float* labels,
+                           void* compute_stream, void* apply_stream);
+int dtf_wd_join(dtf_wd_plan*, void* stream);      /* stream waits for every apply issued so far */
+void dtf_wd_overlap_reset(dtf_wd_plan*);
 /* per-kernel tracing with CUDA events (the reference only prints wall-clock, trainer/task.py:100-102) */
 void dtf_wd_profile_enable(dtf_wd_plan*, int on);
 int dtf_wd_profile_read(dtf_wd_plan*, char* buf, size_t cap);
