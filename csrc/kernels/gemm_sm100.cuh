@@ -25,7 +25,7 @@ constexpr int BM = 128;       // rows per CTA tile == UMMA M
 constexpr int BK = 64;        // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;    // fixed for 16-bit inputs
 constexpr int kNumMainThreads = 192;
-constexpr int kNumGatherWarps = 6;
+constexpr int kNumGatherWarps = 12;
 constexpr int kNumGatherThreads = kNumGatherWarps * 32;
 constexpr int kSliceRows = 16;          // rows per gather slice (one warp, 8 x LDG.128 per lane)
 constexpr int kSlicesPerTile = BM / kSliceRows;
@@ -87,7 +87,7 @@ __device__ __forceinline__ void decode_tile(const GemmParams& p, int tile, int& 
 }
 
 template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
-__global__ void __launch_bounds__(GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads, 1)
+__global__ void __launch_bounds__(GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads, 1) __maxnreg__(GATHER ? 104 : 255)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
   using S = GemmSmem<BN, GATHER>;
