@@ -107,3 +107,51 @@ extern "C" int dtf_push_gemm_bf16(const void* dY, long long lddy, const void* W,
   a.bn = 256;
   return launch_gemm_kmn(a);
 }
+
+// Fused dense-parameter pull: D = act(A W^T + bias) where W [N,K] is row-sharded over `shards`
+// ranks (shard s holds rows [s*rows_per_shard, (s+1)*rows_per_shard)) and every shard pointer may be
+// a peer-mapped address.  The TMA producer of each N-tile loads its B rows directly from the owning
+// rank through that rank's tensor map, i.e. the all-gather happens inside the GEMM and no gathered
+// copy of W is ever materialised.  maps_scratch: shards * 128 bytes of device memory (64-byte aligned)
+// that receives the encoded tensor maps.  SURVEY.md 2E row K1b.
+extern "C" int dtf_allgather_gemm_bf16(const void* A, long long lda, const void* const* W_shards, int shards,
+                                       int rows_per_shard, long long ldw, void* D, long long ldd, int M, int N, int K,
+                                       const float* bias, int relu, void* mask_out, long long ldmask,
+                                       void* maps_scratch, void* stream) {
+  if (shards < 1 || shards > 16 || rows_per_shard <= 0 || static_cast<long long>(shards) * rows_per_shard < N) {
+    set_error("dtf_allgather_gemm_bf16: %d shards x %d rows do not cover N=%d (at most 16 shards)", shards,
+              rows_per_shard, N);
+    return -2;
+  }
+  int bn = 256;
+  while (bn > 64 && (rows_per_shard % bn) != 0) bn >>= 1;
+  if (rows_per_shard % bn != 0) {
+    set_error("dtf_allgather_gemm_bf16: rows_per_shard=%d must be a multiple of 64", rows_per_shard);
+    return -2;
+  }
+  if (bias == nullptr || maps_scratch == nullptr || (reinterpret_cast<uintptr_t>(maps_scratch) & 63)) {
+    set_error("dtf_allgather_gemm_bf16: bias and a 64-byte aligned maps_scratch are required");
+    return -2;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CUtensorMap maps[16];
+  for (int s = 0; s < shards; ++s) {
+    const int rows = (s + 1) * rows_per_shard <= N ? rows_per_shard : (N - s * rows_per_shard > 0 ? N - s * rows_per_shard : 0);
+    if (rows == 0) { maps[s] = maps[0]; continue; }
+    if (!make_tmap_bf16_2d(&maps[s], W_shards[s], (uint64_t)K, (uint64_t)rows, (uint64_t)ldw * 2, BK, bn)) return -1;
+  }
+  DTF_CUDA_OK(cudaMemcpyAsync(maps_scratch, maps, sizeof(CUtensorMap) * shards, cudaMemcpyHostToDevice, st));
+  GemmArgs a{};
+  a.stream = st;
+  a.splits = 1;
+  a.A = A; a.lda = lda; a.B = W_shards[0]; a.ldb = ldw; a.D = D; a.ldd = ldd;
+  a.M = M; a.N = N; a.K = K;
+  a.epi = relu ? EPI_BIAS_RELU_BF16 : EPI_BIAS_BF16;
+  a.bias = bias;
+  a.mask_out = relu ? reinterpret_cast<uint32_t*>(mask_out) : nullptr;
+  a.ldmask = ldmask;
+  a.bn = bn;
+  a.b_maps = reinterpret_cast<const CUtensorMap*>(maps_scratch);
+  a.b_rows_per_shard = rows_per_shard;
+  return launch_gemm_kk(a);
+}

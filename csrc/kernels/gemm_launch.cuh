@@ -23,6 +23,8 @@ struct GemmArgs {
   int slots, dense_cols;
   unsigned int* tile_flags;
   unsigned int* chunk_counter;
+  // fused dense pull (B row-sharded over peers)
+  const CUtensorMap* b_maps; int b_rows_per_shard;
   // fused push
   const unsigned long long* row_dst;
   cudaStream_t stream;
@@ -78,6 +80,7 @@ int launch_gemm_t(const GemmArgs& a) {
   p.slots = a.slots; p.dense_cols = a.dense_cols;
   p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter;
   p.row_dst = a.row_dst;
+  p.b_maps = a.b_maps; p.b_rows_per_shard = a.b_rows_per_shard;
   const int tiles = p.m_tiles * p.n_tiles * p.splits;
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of CTAs without tiles still pull rows

@@ -58,6 +58,10 @@ struct GemmParams {
   int dense_cols;                     // 64
   unsigned int* tile_flags;           // [m_tiles] arrival counters (8*(slots+1) slices each), zero before launch
   unsigned int* chunk_counter;        // [1] reserved
+  // --- fused dense pull (all-gather + GEMM): B is row-sharded over ranks; tile n reads its rows
+  //     straight from the owning rank through that rank's tensor map (global memory array) ---
+  const CUtensorMap* b_maps;          // [shards] or nullptr
+  int b_rows_per_shard;               // multiple of the N tile
   // --- fused push epilogue: destination of the 128-wide bf16 row for (m, slot) ---
   const unsigned long long* row_dst;  // [M * slots] global addresses (may be peer mailbox)
 };
@@ -179,7 +183,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               tma_load_2d(sa + j * (BK * 128), &tmA, full_bar(s), m_t * BM + j * 64, kb * BK);
           }
           if constexpr (!B_MN) {
-            tma_load_2d(sb, &tmB, full_bar(s), kb * BK, n_t * BN);
+            const void* mapB = &tmB;
+            int nrow = n_t * BN;
+            if (p.b_maps != nullptr) {  // peer-addressed operand: pick the owner's tensor map
+              const int shard = nrow / p.b_rows_per_shard;
+              mapB = p.b_maps + shard;
+              nrow -= shard * p.b_rows_per_shard;
+            }
+            tma_load_2d(sb, mapB, full_bar(s), kb * BK, nrow);
           } else {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)

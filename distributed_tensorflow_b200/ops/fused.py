@@ -62,3 +62,33 @@ def push_gemm(dy: torch.Tensor, w: torch.Tensor, row_dst: torch.Tensor) -> None:
     rc = L.dtf_push_gemm_bf16(_lib.ptr(dy), C.c_longlong(dy.stride(0)), _lib.ptr(w), C.c_longlong(w.stride(0)),
                               _lib.ptr(row_dst), C.c_int(slots), C.c_int(M), C.c_int(K), _lib.stream_ptr())
     _lib.check(rc, "dtf_push_gemm_bf16")
+
+
+def allgather_gemm(x: torch.Tensor, w_shards, bias: torch.Tensor, relu: bool = True, mask_out: torch.Tensor = None):
+    """``act(x @ cat(w_shards).T + bias)`` without materialising the concatenation: every N-tile's TMA
+    loads read their rows of W from the shard that owns them (shards may live in peers' HBM, mapped
+    over NVLink).  ``w_shards``: list of bf16 [rows_per_shard, K] tensors or raw device addresses."""
+    M, K = x.shape
+    ptrs, rows = [], None
+    for s in w_shards:
+        if isinstance(s, torch.Tensor):
+            assert s.dtype == torch.bfloat16 and s.shape[1] == K and s.is_contiguous()
+            rows = s.shape[0] if rows is None else rows
+            assert s.shape[0] == rows
+            ptrs.append(s.data_ptr())
+        else:
+            ptrs.append(int(s[0]))
+            rows = int(s[1]) if rows is None else rows
+    N = rows * len(ptrs)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    scratch = torch.empty(128 * len(ptrs) + 64, dtype=torch.uint8, device=x.device)
+    off = (-scratch.data_ptr()) % 64
+    arr = (C.c_void_p * len(ptrs))(*ptrs)
+    L = _lib.lib()
+    rc = L.dtf_allgather_gemm_bf16(_lib.ptr(x), C.c_longlong(x.stride(0)), arr, C.c_int(len(ptrs)), C.c_int(rows),
+                                   C.c_longlong(K), _lib.ptr(out), C.c_longlong(out.stride(0)), C.c_int(M), C.c_int(N),
+                                   C.c_int(K), _lib.ptr(bias), C.c_int(int(relu)), _lib.ptr(mask_out),
+                                   C.c_longlong(mask_out.stride(0) if mask_out is not None else mask_words(N)),
+                                   C.c_void_p(scratch.data_ptr() + off), _lib.stream_ptr())
+    _lib.check(rc, "dtf_allgather_gemm_bf16")
+    return out

@@ -64,6 +64,17 @@ int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void* dense_x, i
                        void* a_buf, const void* W, long long ldw, const float* bias, void* H, long long ldh,
                        void* mask_out, long long ldmask, int M, int N, int relu, void* scratch, void* stream);
 
+/* Fused dense-parameter pull (all-gather + GEMM): D = act(A W^T + bias) with W [N,K] row-sharded over
+ * `shards` ranks; W_shards is a host array of device pointers (local or peer-mapped), shard s holding
+ * rows [s*rows_per_shard, ...).  Each N-tile's TMA loads come straight from the owning rank's HBM
+ * through that rank's tensor map; no gathered copy of W exists.  rows_per_shard must be a multiple of
+ * 64; maps_scratch = shards*128 bytes of 64-byte aligned device memory.  Replaces the dense variable
+ * read ps->worker of reference trainer/task.py:137. */
+int dtf_allgather_gemm_bf16(const void* A, long long lda, const void* const* W_shards, int shards,
+                            int rows_per_shard, long long ldw, void* D, long long ldd, int M, int N, int K,
+                            const float* bias, int relu, void* mask_out, long long ldmask, void* maps_scratch,
+                            void* stream);
+
 /* Fused gradient push: dA = dY[M,K] * W[K, :slots*128]; the bf16 row of (m, slot) is stored to the
  * address row_dst[m*slots+slot] (0 = skip), e.g. a mailbox entry in the owning rank's HBM.
  * Replaces the worker->ps gradient Send of reference trainer/task.py:138. */

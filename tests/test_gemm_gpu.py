@@ -105,3 +105,36 @@ def test_fused_push_gemm(M, slots, K):
     ref[5, 1] = 0
     assert _rel(got, ref) < 1e-2
     assert mailbox[M * slots:].abs().max() == 0
+
+
+@pytest.mark.parametrize("M,rows,shards,K", [(300, 64, 3, 136), (2048, 256, 4, 1024), (1024, 128, 8, 512)])
+def test_allgather_gemm_reads_row_shards_in_place(M, rows, shards, K):
+    from distributed_tensorflow_b200.ops import fused as F
+    torch.manual_seed(5)
+    x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    ws = [(torch.randn(rows, K, device="cuda") * 0.05).bfloat16() for _ in range(shards)]
+    b = torch.randn(rows * shards, device="cuda") * 0.1
+    y = F.allgather_gemm(x, ws, b, relu=True)
+    ref = torch.relu(x.float() @ torch.cat(ws).float().t() + b)
+    assert _rel(y, ref) < 1e-2
+
+
+def test_allgather_gemm_over_peer_memory():
+    """Half of the weight rows live in another GPU's HBM (direct peer mapping)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import ctypes as C
+    from distributed_tensorflow_b200.ops import _lib
+    from distributed_tensorflow_b200.ops import fused as F
+    torch.cuda.set_device(0)
+    assert _lib.lib().dtf_symm_enable_peer(C.c_int(1)) == 0
+    torch.manual_seed(6)
+    M, rows, K = 1024, 256, 512
+    x = (torch.randn(M, K, device="cuda:0") * 0.5).bfloat16()
+    w0 = (torch.randn(rows, K, device="cuda:0") * 0.05).bfloat16()
+    w1 = (torch.randn(rows, K, device="cuda:1") * 0.05).bfloat16()
+    torch.cuda.synchronize(1)
+    b = torch.zeros(2 * rows, device="cuda:0")
+    y = F.allgather_gemm(x, [w0, (w1.data_ptr(), rows)], b, relu=False)
+    ref = x.float() @ torch.cat([w0, w1.to("cuda:0")]).float().t()
+    assert _rel(y, ref) < 1e-2
