@@ -352,89 +352,6 @@ __device__ __forceinline__ bool mailbox_locate(const MailboxView& mv, const unsi
   return true;
 }
 
-// sync-replica, pass 1: G[row] += grad (local fp32 reductions), mark the row as touched
-__global__ void __launch_bounds__(256)
-wd_sparse_accum_kernel(MailboxView mv, float* __restrict__ G, float* __restrict__ wide_G,
-                       unsigned int* __restrict__ bitmap) {
-  __shared__ unsigned int s_prefix[kMaxWorld + 1];
-  if (threadIdx.x == 0) {
-    unsigned int acc = 0;
-    for (int s = 0; s < mv.world; ++s) {
-      s_prefix[s] = acc;
-      acc += min(mv.count[s], static_cast<unsigned int>(mv.cap));
-    }
-    for (int s = mv.world; s <= kMaxWorld; ++s) s_prefix[s] = acc;
-  }
-  __syncthreads();
-  const long long total = s_prefix[mv.world];
-  const int lane = threadIdx.x & 31;
-  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  for (long long g = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; g < total; g += nwarps) {
-    long long e;
-    if (!mailbox_locate(mv, s_prefix, g, e)) continue;
-    const int row = mv.rows[e];
-    const uint2 raw = *reinterpret_cast<const uint2*>(mv.payload + e * kEmbDim + lane * 4);
-    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
-    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
-    red_add_f32x4(G + static_cast<long long>(row) * kEmbDim + lane * 4, a.x, a.y, b.x, b.y);
-    if (lane == 0) {
-      atomicAdd(wide_G + row, mv.dl[e]);
-      atomicOr(bitmap + (row >> 5), 1u << (row & 31));
-    }
-  }
-}
-
-// sync-replica, pass 2: one optimizer step for every touched row; clears G and the bitmap
-template <int OPT>
-__global__ void __launch_bounds__(256)
-wd_sparse_apply_rows_kernel(unsigned int* __restrict__ bitmap, long long nwords, float* __restrict__ G,
-                            float* __restrict__ wide_G, float* __restrict__ master, float* __restrict__ s1,
-                            float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
-                            float* __restrict__ wide_s1, float* __restrict__ wide_s2, const StepState* __restrict__ stp) {
-  const OptConst oc = stp->oc;
-  const int lane = threadIdx.x & 31;
-  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  for (long long wi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; wi < nwords; wi += nwarps) {
-    unsigned int bits = bitmap[wi];
-    if (bits == 0) continue;
-    __syncwarp();
-    if (lane == 0) bitmap[wi] = 0;
-    while (bits) {
-      const int b = __ffs(bits) - 1;
-      bits &= bits - 1;
-      const long long row = wi * 32 + b;
-      const long long o = row * kEmbDim + lane * 4;
-      float4 g = *reinterpret_cast<float4*>(G + o);
-      float4 w = *reinterpret_cast<float4*>(master + o);
-      float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
-      if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + o);
-      if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + o);
-      opt_update<OPT>(w.x, g.x, a.x, v.x, oc);
-      opt_update<OPT>(w.y, g.y, a.y, v.y, oc);
-      opt_update<OPT>(w.z, g.z, a.z, v.z, oc);
-      opt_update<OPT>(w.w, g.w, a.w, v.w, oc);
-      *reinterpret_cast<float4*>(master + o) = w;
-      if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o) = a;
-      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o) = v;
-      *reinterpret_cast<float4*>(G + o) = make_float4(0, 0, 0, 0);
-      uint2 pk;
-      pk.x = pack_bf16x2(w.x, w.y);
-      pk.y = pack_bf16x2(w.z, w.w);
-      *reinterpret_cast<uint2*>(work + o) = pk;
-      if (lane == 0) {
-        float ww = wide[row], wa = 0.f, wv = 0.f;
-        if (OPT != WD_SGD) wa = wide_s1[row];
-        if (OPT == WD_ADAM) wv = wide_s2[row];
-        opt_update<OPT>(ww, wide_G[row], wa, wv, oc);
-        wide[row] = ww;
-        if (OPT != WD_SGD) wide_s1[row] = wa;
-        if (OPT == WD_ADAM) wide_s2[row] = wv;
-        wide_G[row] = 0.f;
-      }
-    }
-  }
-}
-
 // async (Hogwild): every mailbox entry is applied on its own, straight onto the shard, with no
 // duplicate handling and no locks -- concurrent entries for one row race exactly like
 // use_locking=False in the reference's Apply* ops.
@@ -510,6 +427,106 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
         if (OPT != WD_SGD) wide_s1[row[u]] = wa[u];
         if (OPT == WD_ADAM) wide_s2[row[u]] = wv[u];
       }
+    }
+  }
+}
+
+// ---- sync-replica, version 2: count first, then apply in one pass ---------------------------------
+// row_state[row] (64 bit): low word = number of mailbox entries of this step that target the row,
+// high word = how many of them have been folded in so far.  Rows with a single contribution
+// (the common case) are updated straight from the mailbox; contributions to a shared row are summed
+// in G with fp32 reductions and whichever warp arrives last performs the one optimizer step.
+__global__ void __launch_bounds__(256)
+wd_sparse_count_kernel(MailboxView mv, unsigned long long* __restrict__ row_state) {
+  __shared__ unsigned int s_prefix[kMaxWorld + 1];
+  if (threadIdx.x == 0) {
+    unsigned int acc = 0;
+    for (int s = 0; s < mv.world; ++s) {
+      s_prefix[s] = acc;
+      acc += min(mv.count[s], static_cast<unsigned int>(mv.cap));
+    }
+    for (int s = mv.world; s <= kMaxWorld; ++s) s_prefix[s] = acc;
+  }
+  __syncthreads();
+  const long long total = s_prefix[mv.world];
+  for (long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; g < total;
+       g += static_cast<long long>(gridDim.x) * blockDim.x) {
+    long long e;
+    if (mailbox_locate(mv, s_prefix, g, e)) atomicAdd(row_state + mv.rows[e], 1ull);
+  }
+}
+
+template <int OPT>
+__global__ void __launch_bounds__(256)
+wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row_state, float* __restrict__ G,
+                            float* __restrict__ wide_G, float* __restrict__ master, float* __restrict__ s1,
+                            float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
+                            float* __restrict__ wide_s1, float* __restrict__ wide_s2, const StepState* __restrict__ stp) {
+  const OptConst oc = stp->oc;
+  __shared__ unsigned int s_prefix[kMaxWorld + 1];
+  if (threadIdx.x == 0) {
+    unsigned int acc = 0;
+    for (int s = 0; s < mv.world; ++s) {
+      s_prefix[s] = acc;
+      acc += min(mv.count[s], static_cast<unsigned int>(mv.cap));
+    }
+    for (int s = mv.world; s <= kMaxWorld; ++s) s_prefix[s] = acc;
+  }
+  __syncthreads();
+  const long long total = s_prefix[mv.world];
+  const int lane = threadIdx.x & 31;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += nwarps) {
+    long long e;
+    if (!mailbox_locate(mv, s_prefix, gi, e)) continue;
+    const long long row = mv.rows[e];
+    const long long o = row * kEmbDim + lane * 4;
+    const uint2 raw = *reinterpret_cast<const uint2*>(mv.payload + e * kEmbDim + lane * 4);
+    const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+    const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+    float4 g = make_float4(ga.x, ga.y, gb.x, gb.y);
+    float gw = mv.dl[e];
+    const unsigned int n = static_cast<unsigned int>(__ldcg(row_state + row) & 0xFFFFFFFFull);
+    if (n > 1) {
+      // shared row: fold this contribution into G, the last arriver takes the sum
+      red_add_f32x4(G + o, g.x, g.y, g.z, g.w);
+      if (lane == 0) atomicAdd(wide_G + row, gw);
+      __threadfence();
+      __syncwarp();
+      unsigned int arrived = 0;
+      if (lane == 0) arrived = static_cast<unsigned int>(atomicAdd(row_state + row, 1ull << 32) >> 32);
+      arrived = __shfl_sync(0xffffffffu, arrived, 0);
+      if (arrived + 1 != n) continue;
+      __threadfence();
+      g = __ldcg(reinterpret_cast<const float4*>(G + o));
+      gw = __ldcg(wide_G + row);
+      *reinterpret_cast<float4*>(G + o) = make_float4(0, 0, 0, 0);
+      if (lane == 0) wide_G[row] = 0.f;
+    }
+    float4 w = *reinterpret_cast<float4*>(master + o);
+    float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
+    if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + o);
+    if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + o);
+    opt_update<OPT>(w.x, g.x, a.x, v.x, oc);
+    opt_update<OPT>(w.y, g.y, a.y, v.y, oc);
+    opt_update<OPT>(w.z, g.z, a.z, v.z, oc);
+    opt_update<OPT>(w.w, g.w, a.w, v.w, oc);
+    *reinterpret_cast<float4*>(master + o) = w;
+    if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o) = a;
+    if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o) = v;
+    uint2 pk;
+    pk.x = pack_bf16x2(w.x, w.y);
+    pk.y = pack_bf16x2(w.z, w.w);
+    *reinterpret_cast<uint2*>(work + o) = pk;
+    if (lane == 0) {
+      float ww = wide[row], wa = 0.f, wv = 0.f;
+      if (OPT != WD_SGD) wa = wide_s1[row];
+      if (OPT == WD_ADAM) wv = wide_s2[row];
+      opt_update<OPT>(ww, gw, wa, wv, oc);
+      wide[row] = ww;
+      if (OPT != WD_SGD) wide_s1[row] = wa;
+      if (OPT == WD_ADAM) wide_s2[row] = wv;
+      row_state[row] = 0ull;   // ready for the next step
     }
   }
 }

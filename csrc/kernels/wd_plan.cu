@@ -43,8 +43,7 @@ struct dtf_wd_plan {
   // local buffers
   float *emb_master = nullptr, *emb_s1 = nullptr, *emb_s2 = nullptr, *G = nullptr;
   float *wide_s1 = nullptr, *wide_s2 = nullptr, *wide_G = nullptr;
-  unsigned int* bitmap = nullptr;
-  long long bitmap_words = 0;
+  unsigned long long* row_state = nullptr;   // sync mode: per-row contribution counters
   float *dense_master = nullptr, *dense_s1 = nullptr, *dense_s2 = nullptr;
   __nv_bfloat16 *a_buf = nullptr, *dense_x = nullptr, *H1 = nullptr, *H2 = nullptr, *H3 = nullptr;
   __nv_bfloat16 *dZ1 = nullptr, *dZ2 = nullptr, *dZ3 = nullptr;
@@ -244,8 +243,7 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   if (cfg->sync) {
     ok &= (p->G = p->alloc<float>("emb_grad_accum", ne)) != nullptr;
     ok &= (p->wide_G = p->alloc<float>("wide_grad_accum", sh.rows_local)) != nullptr;
-    p->bitmap_words = (sh.rows_local + 31) / 32;
-    ok &= (p->bitmap = p->alloc<unsigned int>("touched_bitmap", p->bitmap_words)) != nullptr;
+    ok &= (p->row_state = p->alloc<unsigned long long>("row_state", sh.rows_local)) != nullptr;
   }
   ok &= (p->dense_master = p->alloc<float>("dense_master", chunk)) != nullptr;
   if (has1) ok &= (p->dense_s1 = p->alloc<float>("dense_slot1", chunk)) != nullptr;
@@ -538,12 +536,12 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
     grid = static_cast<int>(want > grid ? want : grid);
   }
   if (p->cfg.sync) {
-    wd_sparse_accum_kernel<<<grid, 256, 0, st>>>(mv, p->G, p->wide_G, p->bitmap);
-    mark(p, st, "sparse accum");
-    wd_sparse_apply_rows_kernel<OPT><<<grid, 256, 0, st>>>(p->bitmap, p->bitmap_words, p->G, p->wide_G, p->emb_master,
-                                                           p->emb_s1, p->emb_s2, work, wide, p->wide_s1, p->wide_s2, oc);
+    wd_sparse_count_kernel<<<num_sms() * 4, 256, 0, st>>>(mv, p->row_state);
+    mark(p, st, "sparse count");
+    wd_sparse_apply_sync_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->row_state, p->G, p->wide_G, p->emb_master, p->emb_s1,
+                                                           p->emb_s2, work, wide, p->wide_s1, p->wide_s2, oc);
     count_launch(2);
-    mark(p, st, "sparse apply rows");
+    mark(p, st, "sparse apply (sync)");
   } else {
     wd_sparse_apply_entries_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
                                                               p->wide_s1, p->wide_s2, oc);
