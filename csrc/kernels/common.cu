@@ -1,6 +1,7 @@
 #include "common.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -21,6 +22,15 @@ void set_error(const char* fmt, ...) {
 }
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DTF_PDL");
+    v = (e != nullptr && e[0] == '1') ? 1 : 0;   // off unless DTF_PDL=1, see common.cuh
+  }
+  return v == 1;
+}
 
 int num_sms() {
   static int cached[64] = {0};

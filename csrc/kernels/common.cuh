@@ -26,6 +26,29 @@ inline bool make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner
   return make_tmap_2d(out, base, 2, inner, outer, row_stride_bytes, box_inner, box_outer);
 }
 
+// Launch with the programmatic-stream-serialization attribute (PDL): the kernel may be scheduled while
+// its predecessor in the stream drains; it must execute griddepcontrol.wait before touching memory
+// the predecessor writes.  Measured on the wide-and-deep step (1 x B200): serial eager 0.470 -> 0.445 ms,
+// no change under CUDA-graph replay, and the async mode that overlaps the ps-side apply on a second
+// stream gets slower (0.388 -> 0.438 ms: early-resident dependents take the room the apply blocks use),
+// so the attribute is opt-in: DTF_PDL=1.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+cudaError_t launch_kernel(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                          Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 #define DTF_CUDA_OK(expr)                                                               \
   do {                                                                                  \
     cudaError_t _e = (expr);                                                            \

@@ -27,6 +27,7 @@ struct GemmArgs {
   const CUtensorMap* b_maps; int b_rows_per_shard;
   // fused push
   const unsigned long long* row_dst;
+  bool pdl;   // launch with programmatic stream serialization (step executor)
   cudaStream_t stream;
 };
 
@@ -85,8 +86,7 @@ int launch_gemm_t(const GemmArgs& a) {
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of CTAs without tiles still pull rows
   const int threads = GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads;
-  kern<<<grid, threads, S::kTotal, a.stream>>>(tmA, tmB, tmD, p);
-  DTF_CUDA_OK(cudaGetLastError());
+  DTF_CUDA_OK(launch_kernel(a.pdl, kern, dim3(grid), dim3(threads), S::kTotal, a.stream, tmA, tmB, tmD, p));
   count_launch();
   return 0;
 }

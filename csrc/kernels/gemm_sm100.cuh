@@ -144,6 +144,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the tail of the
+  // previous kernel in the stream; its results are needed only from here on
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // =============================== TMA producer ===============================

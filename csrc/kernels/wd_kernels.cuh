@@ -141,6 +141,8 @@ __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V,
                                 unsigned long long* __restrict__ row_dst, unsigned long long* __restrict__ dl_dst) {
   __shared__ unsigned int s_cnt[kMaxWorld];
   __shared__ unsigned int s_base[kMaxWorld];
+  pdl_launch_dependents();
+  pdl_wait();
   if (threadIdx.x < kMaxWorld) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -172,6 +174,8 @@ __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V,
 
 __global__ void wd_dense_pad_kernel(const float* __restrict__ raw, __nv_bfloat16* __restrict__ out, int B, int dense_in,
                                     int dense_pad) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int n = B * dense_pad;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = i / dense_pad, c = i % dense_pad;
@@ -193,6 +197,8 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
                float* __restrict__ dlogit, __nv_bfloat16* __restrict__ dz3, float* __restrict__ g_small,
                float* __restrict__ loss_acc, float* __restrict__ prob_out) {
   extern __shared__ float s_red[];  // [8][H3 + 2] (train only)
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -299,6 +305,8 @@ __global__ void __launch_bounds__(256)
 wd_colsum_kernel(const __nv_bfloat16* __restrict__ x, int M, int N, long long ld, int rows_per_block,
                  float* __restrict__ out) {
   __shared__ float s[8][256];
+  pdl_launch_dependents();
+  pdl_wait();
   const int cg = threadIdx.x & 31, rg = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cg * 8;
   const int r0 = blockIdx.y * rows_per_block;

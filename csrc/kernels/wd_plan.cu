@@ -97,6 +97,8 @@ struct dtf_wd_plan {
 // zero fill by kernel instead of cudaMemsetAsync: memset nodes on IPC-exported (peer-mapped) memory
 // made CUDA-graph replays of the multi-rank step slow
 __global__ void wd_zero_kernel(uint4* __restrict__ p, size_t n16) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n16;
        i += static_cast<size_t>(gridDim.x) * blockDim.x)
     p[i] = make_uint4(0, 0, 0, 0);
@@ -106,8 +108,7 @@ static int zero_fill(void* ptr, size_t bytes, cudaStream_t st) {
   int grid = static_cast<int>((n16 + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   if (grid < 1) grid = 1;
-  wd_zero_kernel<<<grid, 256, 0, st>>>(static_cast<uint4*>(ptr), n16);
-  DTF_CUDA_OK(cudaGetLastError());
+  DTF_CUDA_OK(launch_kernel(true, wd_zero_kernel, dim3(grid), dim3(256), 0, st, static_cast<uint4*>(ptr), n16));
   count_launch();
   return 0;
 }
@@ -411,6 +412,7 @@ static GemmArgs base_args(cudaStream_t st) {
   GemmArgs a{};
   a.stream = st;
   a.splits = 1;
+  a.pdl = true;
   return a;
 }
 
@@ -420,11 +422,10 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   const int n = sh.B * sh.F;
   mark(p, st, "begin");
   if (zero_fill(p->zero_region, p->zero_bytes, st) != 0) return -1;
-  wd_route_kernel<<<(n + 255) / 256, 256, 0, st>>>(ids, n, sh.V, p->pt, p->sl, sh.cap, p->cnt, p->row_src, p->wide_src,
-                                                   p->row_dst, p->dl_dst);
-  wd_dense_pad_kernel<<<(sh.B * sh.dense_pad + 255) / 256, 256, 0, st>>>(dense_raw, p->dense_x, sh.B, sh.dense_in,
-                                                                         sh.dense_pad);
-  DTF_CUDA_OK(cudaGetLastError());
+  DTF_CUDA_OK(launch_kernel(true, wd_route_kernel, dim3((n + 255) / 256), dim3(256), 0, st, ids, n, sh.V, p->pt, p->sl,
+                            sh.cap, p->cnt, p->row_src, p->wide_src, p->row_dst, p->dl_dst));
+  DTF_CUDA_OK(launch_kernel(true, wd_dense_pad_kernel, dim3((sh.B * sh.dense_pad + 255) / 256), dim3(256), 0, st,
+                            dense_raw, p->dense_x, sh.B, sh.dense_in, sh.dense_pad));
   count_launch(2);
   mark(p, st, "route+pad");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
@@ -465,9 +466,10 @@ static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, boo
   if (grid > (sh.B + 7) / 8) grid = (sh.B + 7) / 8;
   if (train) {
     const size_t smem = 8 * (sh.h3 + 2) * sizeof(float);
-    wd_loss_kernel<true><<<grid, 256, smem, st>>>(p->H3, p->m3, p->ldm3, small, off_w4, off_b4, off_wb, p->wide_src,
-                                                  p->dl_dst, labels, sh.B, sh.F, sh.h3, inv_batch, p->dlogit, p->dZ3,
-                                                  g_small, p->loss_acc, nullptr);
+    DTF_CUDA_OK(launch_kernel(true, wd_loss_kernel<true>, dim3(grid), dim3(256), smem, st, p->H3, p->m3,
+                              static_cast<long long>(p->ldm3), small, off_w4, off_b4, off_wb, p->wide_src, p->dl_dst, labels,
+                              sh.B, sh.F, sh.h3, inv_batch, p->dlogit, p->dZ3, g_small, p->loss_acc,
+                              static_cast<float*>(nullptr)));
   } else {
     wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_src, nullptr,
                                                 nullptr, sh.B, sh.F, sh.h3, 0.f, nullptr, nullptr, nullptr, nullptr,
@@ -506,8 +508,7 @@ static int dgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n, const __nv_bflo
 static int colsum(const __nv_bfloat16* x, int M, int N, float* out, cudaStream_t st) {
   const int rpb = 128;
   dim3 grid((N + 255) / 256, (M + rpb - 1) / rpb);
-  wd_colsum_kernel<<<grid, 256, 0, st>>>(x, M, N, N, rpb, out);
-  DTF_CUDA_OK(cudaGetLastError());
+  DTF_CUDA_OK(launch_kernel(true, wd_colsum_kernel, grid, dim3(256), 0, st, x, M, N, static_cast<long long>(N), rpb, out));
   count_launch();
   return 0;
 }
