@@ -586,6 +586,28 @@ int dtf_wd_profile_read(dtf_wd_plan* p, char* buf, size_t cap) {
   return static_cast<int>(out.size());
 }
 
+// Same marks as absolute offsets (microseconds since the first mark): lets marks recorded on the
+// compute stream and on the apply stream be laid on one time line.
+int dtf_wd_profile_read_abs(dtf_wd_plan* p, char* buf, size_t cap) {
+  cudaDeviceSynchronize();
+  std::string out;
+  for (size_t i = 0; i < p->marks.size(); ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, p->marks[0].second, p->marks[i].second);
+    char line[128];
+    snprintf(line, sizeof(line), "%s=%.1f\n", p->marks[i].first.c_str(), ms * 1e3f);
+    out += line;
+  }
+  for (auto& m : p->marks) cudaEventDestroy(m.second);
+  p->marks.clear();
+  if (buf && cap) {
+    const size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+  }
+  return static_cast<int>(out.size());
+}
+
 // forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
 // [B*dense_in], labels f32 [B]
 int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, void* stream_) {

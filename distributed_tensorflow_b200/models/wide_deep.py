@@ -262,7 +262,7 @@ class WideDeepTrainer:
         a, b, c = self._ptrs(ids, dense, labels)
         if overlap is None:
             overlap = not self.cfg.sync
-        if overlap and not self.cfg.sync:
+        if overlap:
             if self._apply_stream is None:
                 self._apply_stream = torch.cuda.Stream(device=self.device)
             _lib.check(self._L.dtf_wd_step_overlapped(self._h, a, b, c, self._stream(),

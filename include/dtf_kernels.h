@@ -179,6 +179,7 @@ void dtf_wd_overlap_reset(dtf_wd_plan*);
 /* per-kernel tracing with CUDA events (the reference only prints wall-clock, trainer/task.py:100-102) */
 void dtf_wd_profile_enable(dtf_wd_plan*, int on);
 int dtf_wd_profile_read(dtf_wd_plan*, char* buf, size_t cap);
+int dtf_wd_profile_read_abs(dtf_wd_plan*, char* buf, size_t cap);  /* offsets from the first mark */
 
 #ifdef __cplusplus
 }

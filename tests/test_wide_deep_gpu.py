@@ -190,3 +190,35 @@ def test_async_hogwild_converges_and_predict_agrees():
     acc = ((p > 0.5).float().cpu() == labels).float().mean().item()
     assert acc > 0.8
     t.close()
+
+
+def test_async_serial_and_overlapped_paths_both_train_and_sync_refuses_overlap():
+    from distributed_tensorflow_b200.ops import _lib
+    g = torch.Generator().manual_seed(1)
+    finals = {}
+    for overlap in (False, True):
+        cfg = _cfg(sync=False, emb_rows=2000, lr=0.1)
+        t = _make(cfg, 1)[0]
+        w_true = torch.tensor([1.0, -1.0, 0.5, 0.0, 0.25])
+        gg = torch.Generator().manual_seed(3)
+        losses = []
+        for s in range(60):
+            ids = torch.randint(0, cfg.emb_rows, (cfg.batch, cfg.slots), generator=gg, dtype=torch.int32)
+            dense = torch.randn(cfg.batch, cfg.dense_in, generator=gg)
+            labels = ((dense @ w_true) > 0).float()
+            t.step(ids.to(t.device), dense.to(t.device), labels.to(t.device), overlap=overlap)
+            losses.append(float(t.last_loss_sum()) / cfg.batch)
+        t.join()
+        torch.cuda.synchronize()
+        assert losses[-1] < 0.7 * losses[0], (overlap, losses[::8])
+        assert t.global_step() == 60
+        finals[overlap] = losses[-1]
+        t.close()
+    assert abs(finals[True] - finals[False]) < 0.15         # one step of staleness does not change the outcome
+    t = _make(_cfg(sync=True), 1)[0]
+    b = _batch(t.cfg, 1, t.device)
+    with pytest.raises(_lib.KernelError, match="sync-replica"):
+        t.step(*b, overlap=True)
+    t.step(*b)                                             # the plain path still works
+    torch.cuda.synchronize()
+    t.close()
