@@ -55,8 +55,13 @@ extern "C" int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void*
 // also left in `a_buf` [M, slots*128 + dense_cols] for the weight-gradient GEMM.  `scratch` is
 // caller-provided device memory of dtf_pull_gemm_scratch_bytes(M) bytes; it is cleared here.
 extern "C" size_t dtf_pull_gemm_scratch_bytes(int M) {
-  return (static_cast<size_t>((M + BM - 1) / BM) + 64) * sizeof(unsigned int);
+  return static_cast<size_t>((M + BM - 1) / BM) * kFlagWords * sizeof(unsigned long long) + 256;
 }
+
+// Debugging hook for bench/pull_trace.py: device buffer (>= 71 000 x 8 bytes) that receives globaltimer
+// stamps of the gather warps and TMA producers of the next fused-pull launches; nullptr switches it off.
+static unsigned long long* g_pull_trace = nullptr;
+extern "C" void dtf_debug_set_pull_trace(void* buf) { g_pull_trace = reinterpret_cast<unsigned long long*>(buf); }
 
 extern "C" int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void* dense_x, int slots, int dense_cols,
                                   void* a_buf, const void* W, long long ldw, const float* bias, void* H,
@@ -86,7 +91,8 @@ extern "C" int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void*
   a.gather = true;
   a.row_src = row_src; a.dense_x = dense_x; a.slots = slots; a.dense_cols = dense_cols;
   a.chunk_counter = reinterpret_cast<unsigned int*>(scratch);
-  a.tile_flags = reinterpret_cast<unsigned int*>(scratch) + 64;
+  a.tile_flags = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(scratch) + 256);
+  a.trace = g_pull_trace;
   a.bn = (N % 256 == 0 || N > 512) ? 256 : 128;
   return launch_gemm_gather(a);
 }

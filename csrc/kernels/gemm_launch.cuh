@@ -21,8 +21,9 @@ struct GemmArgs {
   const unsigned long long* row_src;
   const void* dense_x;
   int slots, dense_cols;
-  unsigned int* tile_flags;
+  unsigned long long* tile_flags;
   unsigned int* chunk_counter;
+  unsigned long long* trace = nullptr;
   // fused dense pull (B row-sharded over peers)
   const CUtensorMap* b_maps; int b_rows_per_shard;
   // fused push
@@ -62,6 +63,10 @@ int launch_gemm_t(const GemmArgs& a) {
   } else {
     tmD = tmA;  // unused by the push epilogue
   }
+  if (GATHER && a.slots + 1 > kFlagWords * 16) {
+    set_error("fused pull: at most %d slots per example (got %d)", kFlagWords * 16 - 1, a.slots);
+    return -2;
+  }
   GemmParams p{};
   p.M = a.M; p.N = a.N; p.K = a.K;
   p.m_tiles = (a.M + BM - 1) / BM;
@@ -79,7 +84,7 @@ int launch_gemm_t(const GemmArgs& a) {
   p.a_buf = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(a.A));
   p.lda_buf = a.lda;
   p.slots = a.slots; p.dense_cols = a.dense_cols;
-  p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter;
+  p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter; p.trace = a.trace;
   p.row_dst = a.row_dst;
   p.b_maps = a.b_maps; p.b_rows_per_shard = a.b_rows_per_shard;
   const int tiles = p.m_tiles * p.n_tiles * p.splits;

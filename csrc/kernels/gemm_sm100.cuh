@@ -26,8 +26,9 @@ constexpr int BK = 64;        // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;    // fixed for 16-bit inputs
 constexpr int kNumMainThreads = 192;
 constexpr int kNumGatherWarps = 12;
-constexpr int kNumGatherThreads = kNumGatherWarps * 32;
+constexpr int kNumGatherThreads = kNumGatherWarps * 32 + 32;   // gather warps + one watcher warp
 constexpr int kSliceRows = 16;          // rows per gather slice (one warp, 8 x LDG.128 per lane)
+constexpr int kFlagWords = 4;           // 64-bit words of 16 chunk counters per row-tile: slots + 1 <= 64
 constexpr int kSlicesPerTile = BM / kSliceRows;
 
 enum Epilogue : int {
@@ -56,8 +57,9 @@ struct GemmParams {
   long long lda_buf;
   int slots;                          // F
   int dense_cols;                     // 64
-  unsigned int* tile_flags;           // [m_tiles] arrival counters (8*(slots+1) slices each), zero before launch
+  unsigned long long* tile_flags;     // [m_tiles][kFlagWords]: 4-bit arrival counter per (row-tile, chunk), zero before launch
   unsigned int* chunk_counter;        // [1] reserved
+  unsigned long long* trace;          // debugging only (bench/pull_trace.py): globaltimer stamps, nullptr = off
   // --- fused dense pull (all-gather + GEMM): B is row-sharded over ranks; tile n reads its rows
   //     straight from the owning rank through that rank's tensor map (global memory array) ---
   const CUtensorMap* b_maps;          // [shards] or nullptr
@@ -115,12 +117,20 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * kStages + 2 + b); };
   uint8_t* misc = smem + kStages * S::kStageBytes + S::kStagingBytes + S::kGatherBytes;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(misc + 8 * (2 * kStages + 4));
+  const uint32_t ready_addr = bar_base + 8u * (2 * kStages + 4) + 8u;   // fused pull: chunks published by the watcher
   float* bias_smem = reinterpret_cast<float*>(misc + S::kBarBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles * p.splits;
   const int total_kb = (p.K + BK - 1) / BK;
+  // Fused pull: the tiles are dealt over a whole number of row-tile groups per wave, so that wave i of
+  // the GEMM consumes exactly the row-tiles of gather group i (CTAs beyond that only gather).
+  int tile_step = gridDim.x;
+  if constexpr (GATHER) {
+    if (static_cast<int>(gridDim.x) >= p.n_tiles) tile_step = (gridDim.x / p.n_tiles) * p.n_tiles;
+  }
+  const int tile_begin = static_cast<int>(blockIdx.x) < tile_step ? static_cast<int>(blockIdx.x) : num_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -134,6 +144,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(tfull_bar(b), 1);
       mbar_init(tempty_bar(b), 4);  // one arrival per epilogue warp
     }
+    if constexpr (GATHER) st_shared_u32(ready_addr, 0u);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -153,26 +164,43 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // =============================== TMA producer ===============================
     if (lane == 0) {
       uint32_t kiter = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile_begin; tile < num_tiles; tile += tile_step) {
         int m_t, n_t, s_t;
         decode_tile(p, tile, m_t, n_t, s_t);
         const int kb0 = s_t * p.k_blocks_per_split;
         const int kb1 = min(total_kb, kb0 + p.k_blocks_per_split);
+        // Fused pull: k-blocks become loadable chunk by chunk (one slot = 128 columns = 2 k-blocks, the
+        // dense block last) as the gather warps of the grid deliver them, so the MMAs of a tile run
+        // right behind its gather instead of after it.
+        int ready_kb = kb1;
         if constexpr (GATHER) {
-          // wait until every chunk of this row-tile has been gathered into a_buf
-          // relaxed polling with back-off (an acquire load per poll would flush L1 every time), then
-          // one acquire fence and the generic->async proxy fence before TMA reads the rows
-          const unsigned int need = static_cast<unsigned int>(kSlicesPerTile * (p.slots + 1));
-          unsigned int v;
-          for (;;) {
-            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.tile_flags + m_t) : "memory");
-            if (v >= need) break;
-            __nanosleep(64);
-          }
-          asm volatile("fence.acq_rel.gpu;" ::: "memory");
-          asm volatile("fence.proxy.async;" ::: "memory");
+          ready_kb = kb0;
+          if (p.trace) p.trace[65536 + (blockIdx.x * 8 + (tile / tile_step)) * 4 + 0] = globaltimer_ns();
         }
         for (int kb = kb0; kb < kb1; ++kb, ++kiter) {
+          if constexpr (GATHER) {
+            if (kb >= ready_kb) {
+              // the watcher warp polls the global arrival counters, performs the gpu-scope acquire
+              // and publishes "chunks complete" in shared memory; this thread only pays a shared-memory
+              // acquire load and the generic->async proxy fence before TMA reads the rows
+              const int chunks = p.slots + 1;
+              const int fneed = min(kb / (128 / BK), p.slots);
+              const uint32_t base = static_cast<uint32_t>(tile / tile_step) * chunks;
+              uint32_t r;
+              for (;;) {
+                r = ld_acquire_cta_shared_u32(ready_addr);
+                if (r > base + fneed) break;
+                __nanosleep(20);
+              }
+              const int c = min(static_cast<int>(r - base), chunks);
+              ready_kb = (c >= chunks) ? kb1 : c * (128 / BK);
+              asm volatile("fence.proxy.async;" ::: "memory");
+              if (p.trace && ready_kb == kb1) {
+                p.trace[65536 + (blockIdx.x * 8 + (tile / tile_step)) * 4 + 1] = globaltimer_ns();
+                p.trace[65536 + (blockIdx.x * 8 + (tile / tile_step)) * 4 + 3] = static_cast<unsigned long long>(m_t);
+              }
+            }
+          }
           const int s = kiter % kStages;
           const uint32_t ph = (kiter / kStages) & 1;
           mbar_wait(empty_bar(s), ph ^ 1);
@@ -209,7 +237,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
       uint32_t kiter = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile_begin; tile < num_tiles; tile += tile_step, ++it) {
         int m_t, n_t, s_t;
         decode_tile(p, tile, m_t, n_t, s_t);
         const int kb0 = s_t * p.k_blocks_per_split;
@@ -250,7 +278,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const uint32_t stg = staging_base + q * S::kStagingPerWarp;
     const uint32_t my_row_smem = stg + lane * kPitch;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile_begin; tile < num_tiles; tile += tile_step, ++it) {
       int m_t, n_t, s_t;
       decode_tile(p, tile, m_t, n_t, s_t);
       const int buf = it & 1;
@@ -376,90 +404,160 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tma_store_wait_all();
   } else {
     // =============================== gather warps (fused pull) ===============================
-    // Six independent warps, no shared memory and no intra-CTA synchronisation.  The work is cut
-    // into slices of 16 rows x one slot (4 KB): a warp loads the 16 row addresses, issues 8
-    // LDG.128 per lane straight from the owning rank's HBM (local, or a peer's over NVLink),
-    // stores them into the GEMM operand buffer and bumps the row-tile's arrival counter.  Two
-    // slices are processed together so that 16 x 16 B per lane (8 KB per warp, 48 KB per SM) are in
-    // flight -- enough to cover NVLink latency at link rate.  Slices are dealt round-robin over all
-    // gather warps of the grid in row-tile order, so row-tiles complete in the order the MMA warps
-    // consume them.  (Needs every CTA resident: grid <= SM count, one CTA per SM.)
+    // Twelve independent warps, no shared memory and no intra-CTA synchronisation.  The work is cut
+    // into slices of 16 rows x one chunk (one slot = 256 B per row, 4 KB per slice; the dense block is
+    // the last chunk).  A warp loads the 16 row addresses, issues 8 LDG.128 per lane straight from the
+    // owning rank's HBM (local, or a peer's over NVLink), stores them into the GEMM operand buffer
+    // and bumps the 4-bit arrival counter of (row-tile, chunk).  The loads of the next slice are
+    // issued before the previous slice is stored and released (two register sets), so every warp
+    // always has 4 KB in flight.
+    // Order: row-tiles are taken in groups that match one wave of GEMM tiles; inside a group the
+    // slices run chunk-major, so all row-tiles of the wave receive chunk 0, then chunk 1, ... and the
+    // MMAs of the whole wave follow the gather k-block by k-block.  (Needs every CTA resident:
+    // grid <= SM count, one CTA per SM.)
     if constexpr (GATHER) {
+      if (warp == 6 + kNumGatherWarps) {
+        // ------------------------------ watcher ------------------------------
+        // Follows this CTA's tile sequence, polls the 4-bit arrival counters of the current row-tile
+        // (relaxed loads with back-off), and after every advance does the gpu-scope acquire and
+        // publishes the running count of complete chunks for the producer.
+        if (lane == 0) {
+          const int chunks = p.slots + 1;
+          uint32_t published = 0;
+          for (int tile = tile_begin; tile < num_tiles; tile += tile_step) {
+            const int m_t = (tile / p.n_tiles) % p.m_tiles;
+            int c = 0;
+            while (c < chunks) {
+              unsigned long long v;
+              asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];"
+                           : "=l"(v)
+                           : "l"(p.tile_flags + static_cast<long long>(m_t) * kFlagWords + (c >> 4))
+                           : "memory");
+              int c2 = c;
+              while (c2 < chunks && (c2 >> 4) == (c >> 4) && ((v >> ((c2 & 15) * 4)) & 15ull) == kSlicesPerTile) ++c2;
+              if (c2 > c) {
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+                published += static_cast<uint32_t>(c2 - c);
+                c = c2;
+                st_release_cta_shared_u32(ready_addr, published);
+              } else {
+                __nanosleep(32);
+              }
+            }
+          }
+        }
+      } else {
       const int gw = warp - 6;
       const int chunks_per_tile = p.slots + 1;
       const long long total_slices = static_cast<long long>(p.m_tiles) * chunks_per_tile * kSlicesPerTile;
       const long long stride = static_cast<long long>(gridDim.x) * kNumGatherWarps;
       const int dense_pieces = p.dense_cols / 8;  // 16-byte pieces per dense row
-      for (long long s0 = static_cast<long long>(blockIdx.x) * kNumGatherWarps + gw; s0 < total_slices; s0 += 2 * stride) {
-        uint4 v[2][8];
-        int mt[2];
+      const int group_tiles = max(1, tile_step / p.n_tiles);
+      const long long group_slices = static_cast<long long>(group_tiles) * chunks_per_tile * kSlicesPerTile;
+      const unsigned long long fallback_src = reinterpret_cast<unsigned long long>(p.row_src);
+      const long long first = static_cast<long long>(blockIdx.x) * kNumGatherWarps + gw;
+      int trace_it = 0;
+
+      // slice index -> (row-tile, chunk, first row)
+      auto locate = [&](long long sl, int& m_t, int& f, int& row0) {
+        const int g = static_cast<int>(sl / group_slices);
+        const int r = static_cast<int>(sl - g * group_slices);
+        const int m_base = g * group_tiles;
+        const int gsize = min(group_tiles, p.m_tiles - m_base) * kSlicesPerTile;
+        f = r / gsize;
+        const int rr = r - f * gsize;
+        m_t = m_base + rr / kSlicesPerTile;
+        row0 = m_t * BM + (rr % kSlicesPerTile) * kSliceRows;
+      };
+      auto issue = [&](uint4 (&v)[8], int f, int row0) {
+        if (f < p.slots) {
+          // lanes 0..15 fetch the 16 row addresses once; every step broadcasts the one it needs, so
+          // the eight 16-byte row loads of a lane are issued back to back.  Rows past M and null
+          // addresses read a harmless local location instead of being predicated off: a predicated
+          // load has to merge with the old register value, which serialises the loads.
+          unsigned long long my_src = fallback_src;
+          if (lane < kSliceRows && row0 + lane < p.M) {
+            const unsigned long long a = __ldg(p.row_src + static_cast<long long>(row0 + lane) * p.slots + f);
+            if (a != 0ull) my_src = a;
+          }
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const long long sl = s0 + h * stride;
-          mt[h] = -1;
-          if (sl >= total_slices) continue;
-          const int chunk = static_cast<int>(sl / kSlicesPerTile), part = static_cast<int>(sl % kSlicesPerTile);
-          const int m_t = chunk / chunks_per_tile, f = chunk % chunks_per_tile;
-          mt[h] = m_t;
-          const int row0 = m_t * BM + part * kSliceRows;
-          if (f < p.slots) {
-            // lanes 0..15 fetch the 16 row addresses once; every step broadcasts the one it needs,
-            // so the eight 16-byte row loads of a lane are issued back to back
-            unsigned long long my_src = 0ull;
-            if (lane < kSliceRows && row0 + lane < p.M)
-              my_src = __ldg(p.row_src + static_cast<long long>(row0 + lane) * p.slots + f);
+          for (int u = 0; u < 8; ++u) {
+            const int pc = u * 32 + lane;
+            const unsigned long long src = __shfl_sync(0xffffffffu, my_src, pc >> 4);
+            v[u] = ld_global_nc_v4(reinterpret_cast<const uint8_t*>(src) + (pc & 15) * 16);
+          }
+        } else {
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const int pc = u * 32 + lane;
-              const unsigned long long src = __shfl_sync(0xffffffffu, my_src, pc >> 4);
-              if (src != 0ull) v[h][u] = ld_global_nc_v4(reinterpret_cast<const uint8_t*>(src) + (pc & 15) * 16);
-            }
-          } else {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int pc = u * 32 + lane;
-              const int r = row0 + pc / dense_pieces;
-              if (pc < kSliceRows * dense_pieces && r < p.M)
-                v[h][u] = ld_global_nc_v4(p.dense_x + static_cast<long long>(r) * p.dense_cols + (pc % dense_pieces) * 8);
-            }
+          for (int u = 0; u < 4; ++u) {
+            const int pc = u * 32 + lane;
+            const int r = row0 + pc / max(dense_pieces, 1);
+            if (pc < kSliceRows * dense_pieces && r < p.M)
+              v[u] = ld_global_nc_v4(p.dense_x + static_cast<long long>(r) * p.dense_cols + (pc % dense_pieces) * 8);
           }
         }
+      };
+      auto retire = [&](const uint4 (&v)[8], int m_t, int f, int row0) {
+        unsigned long long* tr = nullptr;
+        if (p.trace && lane == 0 && trace_it < 8) {
+          tr = p.trace + ((static_cast<long long>(blockIdx.x) * kNumGatherWarps + gw) * 8 + trace_it) * 4;
+          tr[0] = globaltimer_ns();
+        }
+        if (f < p.slots) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const long long sl = s0 + h * stride;
-          if (sl >= total_slices) continue;
-          const int chunk = static_cast<int>(sl / kSlicesPerTile), part = static_cast<int>(sl % kSlicesPerTile);
-          const int m_t = chunk / chunks_per_tile, f = chunk % chunks_per_tile;
-          const int row0 = m_t * BM + part * kSliceRows;
-          if (f < p.slots) {
+          for (int u = 0; u < 8; ++u) {
+            const int pc = u * 32 + lane;
+            const int r = row0 + (pc >> 4);
+            if (r < p.M)
+              st_global_v4(reinterpret_cast<uint8_t*>(p.a_buf + static_cast<long long>(r) * p.lda_buf + f * 128) + (pc & 15) * 16,
+                           v[u].x, v[u].y, v[u].z, v[u].w);
+          }
+        } else {
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const int pc = u * 32 + lane;
-              const int r = row0 + (pc >> 4);
-              if (r < p.M)
-                st_global_v4(reinterpret_cast<uint8_t*>(p.a_buf + static_cast<long long>(r) * p.lda_buf + f * 128) + (pc & 15) * 16,
-                             v[h][u].x, v[h][u].y, v[h][u].z, v[h][u].w);
-            }
-          } else {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int pc = u * 32 + lane;
-              const int r = row0 + pc / dense_pieces;
-              if (pc < kSliceRows * dense_pieces && r < p.M)
-                st_global_v4(p.a_buf + static_cast<long long>(r) * p.lda_buf + p.slots * 128 + (pc % dense_pieces) * 8,
-                             v[h][u].x, v[h][u].y, v[h][u].z, v[h][u].w);
-            }
+          for (int u = 0; u < 4; ++u) {
+            const int pc = u * 32 + lane;
+            const int r = row0 + pc / max(dense_pieces, 1);
+            if (pc < kSliceRows * dense_pieces && r < p.M)
+              st_global_v4(p.a_buf + static_cast<long long>(r) * p.lda_buf + p.slots * 128 + (pc % dense_pieces) * 8,
+                           v[u].x, v[u].y, v[u].z, v[u].w);
           }
         }
+        if (tr) tr[1] = globaltimer_ns();   // loads consumed, stores issued
         // __syncwarp orders the lanes' stores before lane 0's release, which is cumulative
         __syncwarp();
-        if (lane == 0) {
-#pragma unroll
-          for (int h = 0; h < 2; ++h)
-            if (mt[h] >= 0)
-              asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.tile_flags + mt[h]) : "memory");
+        if (lane == 0)
+          asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p.tile_flags + static_cast<long long>(m_t) * kFlagWords + (f >> 4)),
+                       "l"(1ull << ((f & 15) * 4))
+                       : "memory");
+        if (tr) tr[2] = globaltimer_ns();
+        ++trace_it;
+      };
+
+      if (first < total_slices) {
+        uint4 va[8], vb[8];
+        int ma, fa, ra, mb, fb, rb;
+        long long s0 = first;
+        locate(s0, ma, fa, ra);
+        issue(va, fa, ra);
+        for (;;) {
+          const long long s1 = s0 + stride;
+          const bool have1 = s1 < total_slices;
+          if (have1) {
+            locate(s1, mb, fb, rb);
+            issue(vb, fb, rb);
+          }
+          retire(va, ma, fa, ra);
+          if (!have1) break;
+          s0 = s1 + stride;
+          const bool have2 = s0 < total_slices;
+          if (have2) {
+            locate(s0, ma, fa, ra);
+            issue(va, fa, ra);
+          }
+          retire(vb, mb, fb, rb);
+          if (!have2) break;
         }
       }
+      }  // gather warp
     }
   }
 

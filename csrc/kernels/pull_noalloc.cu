@@ -1,13 +1,13 @@
 // dtf_pull_gemm_bf16_noalloc: the fused pull (embedding gather + GEMM-1) for callers that must
 // not allocate device memory.
 //
-// The ordinary entry point, dtf_pull_gemm_bf16, asks its caller for a scratch buffer (one arrival
-// counter per 128-row tile plus a chunk-claim counter).  Some callers have nowhere to get one: a
+// The ordinary entry point, dtf_pull_gemm_bf16, asks its caller for a scratch buffer (32 bytes of
+// arrival counters per 128-row tile plus a 256-byte header).  Some callers have nowhere to get one: a
 // serving process that handed the whole device to its own memory pool when it started, a plug-in
 // living inside such a process, or a latency-critical request path where cudaMalloc's device-wide
 // synchronisation and unbounded duration are not acceptable.  For them the scratch lives here, in a
 // file-scope __device__ array that is part of the library image: it costs kScratchWords * 4 bytes
-// (about 32 KiB) on every GPU that loads the library, from load until the process exits, and it
+// (about 256 KiB) on every GPU that loads the library, from load until the process exits, and it
 // caps the problem at kMaxRows rows per call.
 //
 // Rules that follow from sharing one array:
@@ -33,7 +33,7 @@ namespace {
 
 constexpr int kMaxRows = 1 << 20;                          // 1,048,576 rows per call
 constexpr int kMaxTiles = kMaxRows / BM;                   // 8192 row tiles
-constexpr int kScratchWords = kMaxTiles + 64;              // word 0: chunk counter, words 64..: tile flags
+constexpr int kScratchWords = kMaxTiles * 8 + 64;          // word 0: reserved counter, words 64..: 32 bytes of chunk counters per tile
 constexpr int kMaxDevices = 64;
 
 static __device__ __align__(256) unsigned int g_pull_scratch[kScratchWords];
@@ -94,7 +94,7 @@ extern "C" int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, con
   if (rc != 0) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // the array keeps the previous call's counters: clear exactly what this call will use
-  const size_t used_words = static_cast<size_t>((M + BM - 1) / BM) + 64;
+  const size_t used_words = static_cast<size_t>((M + BM - 1) / BM) * 8 + 64;
   DTF_CUDA_OK(cudaMemsetAsync(scratch, 0, used_words * sizeof(unsigned int), st));
   GemmArgs a{};
   a.stream = st;
@@ -109,7 +109,7 @@ extern "C" int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, con
   a.gather = true;
   a.row_src = row_src; a.dense_x = dense_x; a.slots = slots; a.dense_cols = dense_cols;
   a.chunk_counter = scratch;
-  a.tile_flags = scratch + 64;
+  a.tile_flags = reinterpret_cast<unsigned long long*>(scratch + 64);
   a.bn = (N % 256 == 0 || N > 512) ? 256 : 128;
   return launch_gemm_gather(a);
 }

@@ -484,57 +484,82 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
   const long long total = s_prefix[mv.world];
   const int lane = threadIdx.x & 31;
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += nwarps) {
-    long long e;
-    if (!mailbox_locate(mv, s_prefix, gi, e)) continue;
-    const long long row = mv.rows[e];
-    const long long o = row * kEmbDim + lane * 4;
-    const uint2 raw = *reinterpret_cast<const uint2*>(mv.payload + e * kEmbDim + lane * 4);
-    const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
-    const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
-    float4 g = make_float4(ga.x, ga.y, gb.x, gb.y);
-    float gw = mv.dl[e];
-    const unsigned int n = static_cast<unsigned int>(__ldcg(row_state + row) & 0xFFFFFFFFull);
-    if (n > 1) {
-      // shared row: fold this contribution into G, the last arriver takes the sum
-      red_add_f32x4(G + o, g.x, g.y, g.z, g.w);
-      if (lane == 0) atomicAdd(wide_G + row, gw);
-      __threadfence();
-      __syncwarp();
-      unsigned int arrived = 0;
-      if (lane == 0) arrived = static_cast<unsigned int>(atomicAdd(row_state + row, 1ull << 32) >> 32);
-      arrived = __shfl_sync(0xffffffffu, arrived, 0);
-      if (arrived + 1 != n) continue;
-      __threadfence();
-      g = __ldcg(reinterpret_cast<const float4*>(G + o));
-      gw = __ldcg(wide_G + row);
-      *reinterpret_cast<float4*>(G + o) = make_float4(0, 0, 0, 0);
-      if (lane == 0) wide_G[row] = 0.f;
+  // two entries per iteration; every load that only depends on the row id (gradient, weights,
+  // slots, row_state) is issued for both before anything is consumed
+  for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += 2 * nwarps) {
+    long long e[2], row[2] = {0, 0}, o[2] = {0, 0};
+    bool ok[2];
+    uint2 raw[2];
+    float4 w[2], a[2], v[2];
+    float dlv[2] = {0.f, 0.f}, ww[2] = {0.f, 0.f}, wa[2] = {0.f, 0.f}, wv[2] = {0.f, 0.f};
+    unsigned int n[2] = {1u, 1u};
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long long g = gi + u * nwarps;
+      ok[u] = g < total && mailbox_locate(mv, s_prefix, g, e[u]);
+      if (ok[u]) row[u] = mv.rows[e[u]];
     }
-    float4 w = *reinterpret_cast<float4*>(master + o);
-    float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
-    if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + o);
-    if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + o);
-    opt_update<OPT>(w.x, g.x, a.x, v.x, oc);
-    opt_update<OPT>(w.y, g.y, a.y, v.y, oc);
-    opt_update<OPT>(w.z, g.z, a.z, v.z, oc);
-    opt_update<OPT>(w.w, g.w, a.w, v.w, oc);
-    *reinterpret_cast<float4*>(master + o) = w;
-    if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o) = a;
-    if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o) = v;
-    uint2 pk;
-    pk.x = pack_bf16x2(w.x, w.y);
-    pk.y = pack_bf16x2(w.z, w.w);
-    *reinterpret_cast<uint2*>(work + o) = pk;
-    if (lane == 0) {
-      float ww = wide[row], wa = 0.f, wv = 0.f;
-      if (OPT != WD_SGD) wa = wide_s1[row];
-      if (OPT == WD_ADAM) wv = wide_s2[row];
-      opt_update<OPT>(ww, gw, wa, wv, oc);
-      wide[row] = ww;
-      if (OPT != WD_SGD) wide_s1[row] = wa;
-      if (OPT == WD_ADAM) wide_s2[row] = wv;
-      row_state[row] = 0ull;   // ready for the next step
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      a[u] = make_float4(0, 0, 0, 0);
+      v[u] = make_float4(0, 0, 0, 0);
+      if (!ok[u]) continue;
+      o[u] = row[u] * kEmbDim + lane * 4;
+      n[u] = static_cast<unsigned int>(__ldcg(row_state + row[u]) & 0xFFFFFFFFull);
+      raw[u] = *reinterpret_cast<const uint2*>(mv.payload + e[u] * kEmbDim + lane * 4);
+      w[u] = *reinterpret_cast<float4*>(master + o[u]);
+      if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
+      if (OPT == WD_ADAM) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
+      if (lane == 0) {
+        dlv[u] = mv.dl[e[u]];
+        ww[u] = wide[row[u]];
+        if (OPT != WD_SGD) wa[u] = wide_s1[row[u]];
+        if (OPT == WD_ADAM) wv[u] = wide_s2[row[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (!ok[u]) continue;
+      const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].x));
+      const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[u].y));
+      float4 g = make_float4(ga.x, ga.y, gb.x, gb.y);
+      float gw = dlv[u];
+      if (n[u] > 1) {
+        // shared row: fold this contribution into G, the last arriver takes the sum.  Weights and
+        // slots of a shared row are only touched by that last arriver, so the copies loaded above
+        // are still current when it gets here.
+        red_add_f32x4(G + o[u], g.x, g.y, g.z, g.w);
+        if (lane == 0) atomicAdd(wide_G + row[u], gw);
+        __threadfence();
+        __syncwarp();
+        unsigned int arrived = 0;
+        if (lane == 0) arrived = static_cast<unsigned int>(atomicAdd(row_state + row[u], 1ull << 32) >> 32);
+        arrived = __shfl_sync(0xffffffffu, arrived, 0);
+        if (arrived + 1 != n[u]) continue;
+        __threadfence();
+        g = __ldcg(reinterpret_cast<const float4*>(G + o[u]));
+        gw = __shfl_sync(0xffffffffu, lane == 0 ? __ldcg(wide_G + row[u]) : 0.f, 0);
+        *reinterpret_cast<float4*>(G + o[u]) = make_float4(0, 0, 0, 0);
+        if (lane == 0) wide_G[row[u]] = 0.f;
+      }
+      opt_update<OPT>(w[u].x, g.x, a[u].x, v[u].x, oc);
+      opt_update<OPT>(w[u].y, g.y, a[u].y, v[u].y, oc);
+      opt_update<OPT>(w[u].z, g.z, a[u].z, v[u].z, oc);
+      opt_update<OPT>(w[u].w, g.w, a[u].w, v[u].w, oc);
+      *reinterpret_cast<float4*>(master + o[u]) = w[u];
+      if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o[u]) = a[u];
+      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
+      uint2 pk;
+      pk.x = pack_bf16x2(w[u].x, w[u].y);
+      pk.y = pack_bf16x2(w[u].z, w[u].w);
+      *reinterpret_cast<uint2*>(work + o[u]) = pk;
+      if (lane == 0) {
+        opt_update<OPT>(ww[u], gw, wa[u], wv[u], oc);
+        wide[row[u]] = ww[u];
+        if (OPT != WD_SGD) wide_s1[row[u]] = wa[u];
+        if (OPT == WD_ADAM) wide_s2[row[u]] = wv[u];
+        row_state[row[u]] = 0ull;   // ready for the next step
+      }
     }
   }
 }

@@ -52,10 +52,11 @@ struct dtf_wd_plan {
   unsigned long long *row_src = nullptr, *wide_src = nullptr, *row_dst = nullptr, *dl_dst = nullptr;
   float* dlogit = nullptr;
   float* prob = nullptr;
-  // zeroed at the start of every step: cnt[kMaxWorld] | chunk_counter | pad | loss_acc[2] | tile_flags[m_tiles]
+  // zeroed at the start of every step: cnt[kMaxWorld] | chunk_counter | pad | loss_acc[2] | tile_flags[m_tiles][kFlagWords] (64-bit)
   unsigned int* zero_region = nullptr;
   size_t zero_bytes = 0;
-  unsigned int *cnt = nullptr, *chunk_counter = nullptr, *tile_flags = nullptr;
+  unsigned int *cnt = nullptr, *chunk_counter = nullptr;
+  unsigned long long* tile_flags = nullptr;
   float* loss_acc = nullptr;
   // optional per-kernel tracing: CUDA events recorded between launches
   bool profile = false;
@@ -127,7 +128,7 @@ static void select_parity(dtf_wd_plan* p, int par) {
   p->cnt = p->zero_region;
   p->chunk_counter = p->zero_region + kMaxWorld;
   p->loss_acc = reinterpret_cast<float*>(p->zero_region + kMaxWorld + 4);
-  p->tile_flags = p->zero_region + kMaxWorld + 8;
+  p->tile_flags = reinterpret_cast<unsigned long long*>(p->zero_region + kMaxWorld + 8);
 }
 
 static int mask_ld(int n) {
@@ -269,10 +270,10 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   ok &= (p->dlogit = p->alloc<float>("dlogit", B)) != nullptr;
   ok &= (p->prob = p->alloc<float>("prob", B)) != nullptr;
   const int m_tiles = (sh.B + BM - 1) / BM;
-  p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles) * 4;   // the allocation below is padded to 16-byte multiples
-  ok &= (p->zero_par[0] = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles + 8)) != nullptr;
+  p->zero_bytes = (kMaxWorld + 4 + 4 + m_tiles * kFlagWords * 2) * 4;   // the allocation below is padded to 16-byte multiples
+  ok &= (p->zero_par[0] = p->alloc<unsigned int>("step_scratch", kMaxWorld + 8 + m_tiles * kFlagWords * 2 + 8)) != nullptr;
   if (cfg->sync) p->zero_par[1] = p->zero_par[0];
-  else ok &= (p->zero_par[1] = p->alloc<unsigned int>("step_scratch1", kMaxWorld + 8 + m_tiles + 8)) != nullptr;
+  else ok &= (p->zero_par[1] = p->alloc<unsigned int>("step_scratch1", kMaxWorld + 8 + m_tiles * kFlagWords * 2 + 8)) != nullptr;
   ok &= (p->state = p->alloc<StepState>("step_state", 1)) != nullptr;
   if (!ok) {
     dtf_wd_destroy(p);
