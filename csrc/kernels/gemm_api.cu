@@ -4,6 +4,35 @@
 
 using namespace dtf;
 
+// CTA-pair mode (tcgen05.mma.cta_group::2, 256 x BN tiles on the two SMs of a TPC): process-wide
+// switch, initialised from DTF_PAIR (default on); shapes / epilogues without a pair instantiation
+// keep using single-CTA tiles.
+static int g_pair_mode = -1;
+namespace dtf {
+bool pair_mode() {
+  if (g_pair_mode < 0) {
+    const char* e = getenv("DTF_PAIR");
+    g_pair_mode = (e == nullptr || e[0] != '0') ? 1 : 0;
+  }
+  return g_pair_mode == 1;
+}
+bool pair_eligible(const GemmArgs& a, int bn) {
+  if (!pair_mode() || a.M < 2 * BM || a.b_maps != nullptr) return false;
+  const int e = a.epi;
+  if (a.gather) return bn == 256 && (e == EPI_BIAS_RELU_BF16 || e == EPI_BIAS_BF16);
+  if (!a.a_mn && !a.b_mn)
+    return ((bn == 256 || bn == 128) && (e == EPI_BF16 || e == EPI_BIAS_BF16 || e == EPI_BIAS_RELU_BF16)) ||
+           (bn == 256 && e == EPI_F32);
+  if (!a.a_mn && a.b_mn)
+    return (bn == 256 && (e == EPI_BF16 || e == EPI_DRELU_BF16 || e == EPI_PUSH_ROWS)) ||
+           (bn == 128 && (e == EPI_BF16 || e == EPI_DRELU_BF16));
+  if (a.a_mn && a.b_mn) return (bn == 256 && (e == EPI_F32 || e == EPI_F32_ATOMIC)) || (bn == 128 && e == EPI_F32_ATOMIC);
+  return false;
+}
+}  // namespace dtf
+extern "C" void dtf_gemm_set_pair_mode(int on) { g_pair_mode = on ? 1 : 0; }
+extern "C" int dtf_gemm_get_pair_mode(void) { return dtf::pair_mode() ? 1 : 0; }
+
 extern "C" int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn,
                              void* D, long long ldd, int M, int N, int K, int epilogue, const float* bias,
                              const void* mask_in, void* mask_out, long long ldmask, int splits, int bn,
@@ -41,7 +70,8 @@ extern "C" int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   a.mask_in = reinterpret_cast<const uint32_t*>(mask_in);
   a.mask_out = reinterpret_cast<uint32_t*>(mask_out);
   a.ldmask = ldmask;
-  a.splits = splits; a.bn = bn;
+  a.splits = splits; a.bn = bn ? bn : choose_bn(M, N, splits);
+  a.pair = pair_eligible(a, a.bn);
   a.stream = reinterpret_cast<cudaStream_t>(stream);
   if (!a.a_mn && !a.b_mn) return launch_gemm_kk(a);
   if (!a.a_mn && a.b_mn) return launch_gemm_kmn(a);
@@ -94,6 +124,7 @@ extern "C" int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void*
   a.tile_flags = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(scratch) + 256);
   a.trace = g_pull_trace;
   a.bn = (N % 256 == 0 || N > 512) ? 256 : 128;
+  a.pair = pair_eligible(a, a.bn);
   return launch_gemm_gather(a);
 }
 
@@ -111,6 +142,7 @@ extern "C" int dtf_push_gemm_bf16(const void* dY, long long lddy, const void* W,
   a.A = dY; a.lda = lddy; a.B = W; a.ldb = ldw; a.b_mn = true;
   a.M = M; a.N = slots * 128; a.K = K; a.epi = EPI_PUSH_ROWS; a.row_dst = row_dst; a.slots = slots;
   a.bn = 256;
+  a.pair = pair_eligible(a, a.bn);
   return launch_gemm_kmn(a);
 }
 

@@ -29,13 +29,14 @@ struct GemmArgs {
   // fused push
   const unsigned long long* row_dst;
   bool pdl;   // launch with programmatic stream serialization (step executor)
+  bool pair = false;   // CTA pairs (cta_group::2, 256 x BN tiles); BN = 256 or 128 only
   cudaStream_t stream;
 };
 
-template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
+template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER, int CTAS = 1>
 int launch_gemm_t(const GemmArgs& a) {
-  using S = GemmSmem<BN, GATHER>;
-  auto kern = gemm_sm100_kernel<BN, A_MN, B_MN, EPI, GATHER>;
+  using S = GemmSmem<BN, GATHER, CTAS>;
+  auto kern = gemm_sm100_kernel<BN, A_MN, B_MN, EPI, GATHER, CTAS>;
   static bool attr_set[64] = {false};
   int dev = 0;
   DTF_CUDA_OK(cudaGetDevice(&dev));
@@ -50,7 +51,7 @@ int launch_gemm_t(const GemmArgs& a) {
     if (!make_tmap_bf16_2d(&tmA, a.A, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda * 2, 64, BK)) return -1;
   }
   if (!B_MN) {
-    if (!make_tmap_bf16_2d(&tmB, a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb * 2, BK, BN)) return -1;
+    if (!make_tmap_bf16_2d(&tmB, a.B, (uint64_t)a.K, (uint64_t)a.N, (uint64_t)a.ldb * 2, BK, BN / CTAS)) return -1;
   } else {
     if (!make_tmap_bf16_2d(&tmB, a.B, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldb * 2, 64, BK)) return -1;
   }
@@ -87,11 +88,12 @@ int launch_gemm_t(const GemmArgs& a) {
   p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter; p.trace = a.trace;
   p.row_dst = a.row_dst;
   p.b_maps = a.b_maps; p.b_rows_per_shard = a.b_rows_per_shard;
-  const int tiles = p.m_tiles * p.n_tiles * p.splits;
-  int grid = tiles < num_sms() ? tiles : num_sms();
-  if (GATHER && grid < num_sms()) grid = num_sms();  // gather warps of CTAs without tiles still pull rows
+  const int tiles = ((p.m_tiles + CTAS - 1) / CTAS) * p.n_tiles * p.splits * CTAS;   // in CTAs
+  const int sms = num_sms() / CTAS * CTAS;
+  int grid = tiles < sms ? tiles : sms;
+  if (GATHER && grid < sms) grid = sms;  // gather warps of CTAs without tiles still pull rows
   const int threads = GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads;
-  DTF_CUDA_OK(launch_kernel(a.pdl, kern, dim3(grid), dim3(threads), S::kTotal, a.stream, tmA, tmB, tmD, p));
+  DTF_CUDA_OK(launch_kernel_cluster(a.pdl, CTAS, kern, dim3(grid), dim3(threads), S::kTotal, a.stream, tmA, tmB, tmD, p));
   count_launch();
   return 0;
 }
@@ -113,6 +115,8 @@ inline int choose_bn(int M, int N, int splits) {
   return best;
 }
 
+bool pair_mode();                                     // DTF_PAIR / dtf_gemm_set_pair_mode
+bool pair_eligible(const GemmArgs& a, int bn);        // is there a CTA-pair instantiation for this launch
 int launch_gemm_kk(const GemmArgs& a);    // A K-major,  B K-major   (forward)
 int launch_gemm_kmn(const GemmArgs& a);   // A K-major,  B MN-major  (dgrad)
 int launch_gemm_mnmn(const GemmArgs& a);  // A MN-major, B MN-major  (wgrad)

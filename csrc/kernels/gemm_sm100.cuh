@@ -68,12 +68,12 @@ struct GemmParams {
   const unsigned long long* row_dst;  // [M * slots] global addresses (may be peer mailbox)
 };
 
-template <int BN, bool GATHER = false>
+template <int BN, bool GATHER = false, int CTAS = 1>
 struct GemmSmem {
   static constexpr int kABytes = BM * BK * 2;  // 16 KB
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBBytes = (BN / CTAS) * BK * 2;   // a CTA pair splits the B rows
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN == 256) ? 4 : ((BN == 128) ? 6 : 8);
+  static constexpr int kStages = (kStageBytes >= 48 * 1024) ? 4 : ((kStageBytes >= 32 * 1024) ? 6 : 8);
   static constexpr int kGatherBytes = 0;
   static constexpr int kStagingPerWarp = 5120;  // 32 rows x 128 B (TMA store) or x 144 B (push)
   static constexpr int kStagingBytes = 4 * kStagingPerWarp;
@@ -85,18 +85,24 @@ struct GemmSmem {
 
 // tile index -> (m, n, split); n fastest so that concurrently running CTAs share A row-tiles.
 __device__ __forceinline__ void decode_tile(const GemmParams& p, int tile, int& m_t, int& n_t,
-                                            int& s_t) {
+                                            int& s_t, int m_units = -1, int ctas = 1, int rank = 0) {
+  if (m_units < 0) m_units = p.m_tiles;
   n_t = tile % p.n_tiles;
   int r = tile / p.n_tiles;
-  m_t = r % p.m_tiles;
-  s_t = r / p.m_tiles;
+  m_t = (r % m_units) * ctas + rank;   // 128-row tile of this CTA (may be past the end for the odd pair)
+  s_t = r / m_units;
 }
 
-template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER>
+// CTAS = 2: the grid is launched in clusters of two CTAs (one TPC); the pair computes a 256 x BN tile
+// with tcgen05.mma.cta_group::2 -- CTA rank r holds rows [128 r, 128 r + 128) of A and rows
+// [BN/2 r, BN/2 r + BN/2) of B, so each SM fills 16 KB + 16 KB per k-block instead of 16 KB + 32 KB.
+template <int BN, bool A_MN, bool B_MN, int EPI, bool GATHER, int CTAS = 1>
 __global__ void __launch_bounds__(GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads, 1) __maxnreg__(GATHER ? 104 : 255)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
-  using S = GemmSmem<BN, GATHER>;
+  using S = GemmSmem<BN, GATHER, CTAS>;
+  constexpr bool kPair = CTAS == 2;
+  constexpr int BNL = BN / CTAS;   // B rows (output columns) staged by one CTA
   constexpr int kStages = S::kStages;
   constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : 2 * BN;  // two accumulator buffers
   constexpr bool kOutF32 = (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC);
@@ -122,15 +128,19 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.m_tiles * p.n_tiles * p.splits;
+  // tiles are 128 x BN per CTA, 256 x BN per CTA pair; a pair walks one tile sequence together
+  const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
+  const int m_units = (p.m_tiles + CTAS - 1) / CTAS;
+  const int num_tiles = m_units * p.n_tiles * p.splits;
   const int total_kb = (p.K + BK - 1) / BK;
+  const int unit_id = blockIdx.x / CTAS;
   // Fused pull: the tiles are dealt over a whole number of row-tile groups per wave, so that wave i of
   // the GEMM consumes exactly the row-tiles of gather group i (CTAs beyond that only gather).
-  int tile_step = gridDim.x;
+  int tile_step = gridDim.x / CTAS;
   if constexpr (GATHER) {
-    if (static_cast<int>(gridDim.x) >= p.n_tiles) tile_step = (gridDim.x / p.n_tiles) * p.n_tiles;
+    if (tile_step >= p.n_tiles) tile_step = (tile_step / p.n_tiles) * p.n_tiles;
   }
-  const int tile_begin = static_cast<int>(blockIdx.x) < tile_step ? static_cast<int>(blockIdx.x) : num_tiles;
+  const int tile_begin = unit_id < tile_step ? unit_id : num_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -142,17 +152,23 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(tfull_bar(b), 1);
-      mbar_init(tempty_bar(b), 4);  // one arrival per epilogue warp
+      mbar_init(tempty_bar(b), 4 * CTAS);  // one arrival per epilogue warp (of both CTAs on the leader)
     }
     if constexpr (GATHER) st_shared_u32(ready_addr, 0u);
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), kTmemCols);
-    tmem_relinquish();
+    if constexpr (kPair) {
+      tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();   // the peer's barriers must exist before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the tail of the
@@ -166,7 +182,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t kiter = 0;
       for (int tile = tile_begin; tile < num_tiles; tile += tile_step) {
         int m_t, n_t, s_t;
-        decode_tile(p, tile, m_t, n_t, s_t);
+        decode_tile(p, tile, m_t, n_t, s_t, m_units, CTAS, cta_rank);
         const int kb0 = s_t * p.k_blocks_per_split;
         const int kb1 = min(total_kb, kb0 + p.k_blocks_per_split);
         // Fused pull: k-blocks become loadable chunk by chunk (one slot = 128 columns = 2 k-blocks, the
@@ -204,42 +220,56 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const int s = kiter % kStages;
           const uint32_t ph = (kiter / kStages) & 1;
           mbar_wait(empty_bar(s), ph ^ 1);
-          mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
+          // pair: both CTAs' loads are counted on the leader's barrier, armed by the leader alone
+          const uint32_t fbar = kPair ? mapa_shared(full_bar(s), 0) : full_bar(s);
+          if (!kPair || cta_rank == 0) mbar_arrive_expect_tx(full_bar(s), CTAS * S::kStageBytes);
+          auto tma_load_2d = [&](uint32_t dst, const void* map, uint32_t bar, int c0, int c1) {
+            if constexpr (kPair) dtf::tma_load_2d_pair(dst, map, bar, c0, c1);
+            else dtf::tma_load_2d(dst, map, bar, c0, c1);
+          };
           const uint32_t sa = smem_base + s * S::kStageBytes;
           const uint32_t sb = sa + S::kABytes;
           if constexpr (!A_MN) {
-            tma_load_2d(sa, &tmA, full_bar(s), kb * BK, m_t * BM);
+            tma_load_2d(sa, &tmA, fbar, kb * BK, m_t * BM);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(sa + j * (BK * 128), &tmA, full_bar(s), m_t * BM + j * 64, kb * BK);
+              tma_load_2d(sa + j * (BK * 128), &tmA, fbar, m_t * BM + j * 64, kb * BK);
           }
           if constexpr (!B_MN) {
             const void* mapB = &tmB;
-            int nrow = n_t * BN;
+            int nrow = n_t * BN + static_cast<int>(cta_rank) * BNL;
             if (p.b_maps != nullptr) {  // peer-addressed operand: pick the owner's tensor map
               const int shard = nrow / p.b_rows_per_shard;
               mapB = p.b_maps + shard;
               nrow -= shard * p.b_rows_per_shard;
             }
-            tma_load_2d(sb, mapB, full_bar(s), kb * BK, nrow);
+            tma_load_2d(sb, mapB, fbar, kb * BK, nrow);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(sb + j * (BK * 128), &tmB, full_bar(s), n_t * BN + j * 64, kb * BK);
+            for (int j = 0; j < BNL / 64; ++j)
+              tma_load_2d(sb + j * (BK * 128), &tmB, fbar, n_t * BN + static_cast<int>(cta_rank) * BNL + j * 64, kb * BK);
           }
         }
       }
     }
   } else if (warp == 1) {
     // =============================== MMA issuer ===============================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && cta_rank == 0) {   // of a pair, only the leader issues MMAs
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CTAS, BN, A_MN, B_MN);
+      auto umma_bf16 = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t acc) {
+        if constexpr (kPair) dtf::umma_bf16_pair(d, ad, bd, id, acc);
+        else dtf::umma_bf16(d, ad, bd, id, acc);
+      };
+      auto umma_commit = [&](uint32_t bar) {
+        if constexpr (kPair) dtf::umma_commit_pair(bar);
+        else dtf::umma_commit(bar);
+      };
       uint32_t kiter = 0;
       int it = 0;
       for (int tile = tile_begin; tile < num_tiles; tile += tile_step, ++it) {
         int m_t, n_t, s_t;
-        decode_tile(p, tile, m_t, n_t, s_t);
+        decode_tile(p, tile, m_t, n_t, s_t, m_units, CTAS, cta_rank);
         const int kb0 = s_t * p.k_blocks_per_split;
         const int kb1 = min(total_kb, kb0 + p.k_blocks_per_split);
         const int buf = it & 1;
@@ -280,7 +310,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     int it = 0;
     for (int tile = tile_begin; tile < num_tiles; tile += tile_step, ++it) {
       int m_t, n_t, s_t;
-      decode_tile(p, tile, m_t, n_t, s_t);
+      decode_tile(p, tile, m_t, n_t, s_t, m_units, CTAS, cta_rank);
       const int buf = it & 1;
       const int n0 = n_t * BN;
       const int row0 = m_t * BM + q * 32;
@@ -399,7 +429,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(buf));
+      if (lane == 0) {
+        if constexpr (kPair) mbar_arrive_cluster(mapa_shared(tempty_bar(buf), 0));
+        else mbar_arrive(tempty_bar(buf));
+      }
     }
     tma_store_wait_all();
   } else {
@@ -425,8 +458,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const int chunks = p.slots + 1;
           uint32_t published = 0;
           for (int tile = tile_begin; tile < num_tiles; tile += tile_step) {
-            const int m_t = (tile / p.n_tiles) % p.m_tiles;
+            int m_t, n_t, s_t;
+            decode_tile(p, tile, m_t, n_t, s_t, m_units, CTAS, cta_rank);
             int c = 0;
+            if (m_t >= p.m_tiles) {   // the odd CTA of the last pair has no rows: nothing to wait for
+              published += static_cast<uint32_t>(chunks);
+              st_release_cta_shared_u32(ready_addr, published);
+              c = chunks;
+            }
             while (c < chunks) {
               unsigned long long v;
               asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];"
@@ -452,7 +491,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const long long total_slices = static_cast<long long>(p.m_tiles) * chunks_per_tile * kSlicesPerTile;
       const long long stride = static_cast<long long>(gridDim.x) * kNumGatherWarps;
       const int dense_pieces = p.dense_cols / 8;  // 16-byte pieces per dense row
-      const int group_tiles = max(1, tile_step / p.n_tiles);
+      const int group_tiles = max(1, tile_step / p.n_tiles) * CTAS;
       const long long group_slices = static_cast<long long>(group_tiles) * chunks_per_tile * kSlicesPerTile;
       const unsigned long long fallback_src = reinterpret_cast<unsigned long long>(p.row_src);
       const long long first = static_cast<long long>(blockIdx.x) * kNumGatherWarps + gw;
@@ -562,10 +601,12 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();   // neither CTA may leave while the other still signals it
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    if constexpr (kPair) tmem_dealloc_pair(tmem_base, kTmemCols);
+    else tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 

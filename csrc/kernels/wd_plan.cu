@@ -409,6 +409,18 @@ int dtf_wd_refresh_embedding(dtf_wd_plan* p, void* stream_) {
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------ step
+// Which GEMMs of the step run on CTA pairs (cta_group::2): bit 0 fused pull, 1 layers 2-3, 2 weight
+// gradients, 3 data gradients, 4 fused push.  DTF_PAIR_MASK overrides the default.
+static int pair_mask() {
+  static int m = -1;
+  if (m < 0) {
+    const char* e = getenv("DTF_PAIR_MASK");
+    m = e ? atoi(e) : (1 | 4 | 16);   // measured: pull 74 -> 70 us, wgrad-1 60 -> 54, push 49 -> 46; the small GEMMs do not gain
+  }
+  return m;
+}
+static void set_pair(GemmArgs& a, int bit) { a.pair = ((pair_mask() >> bit) & 1) && pair_eligible(a, a.bn); }
+
 static GemmArgs base_args(cudaStream_t st) {
   GemmArgs a{};
   a.stream = st;
@@ -438,6 +450,8 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.mask_out = train ? p->m1 : nullptr; a.ldmask = p->ldm1;
   a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
   a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
+  a.bn = 256;
+  set_pair(a, 0);
   if (launch_gemm_gather(a) != 0) return -1;
   mark(p, st, "pull+gemm1");
   // layers 2, 3
@@ -445,11 +459,15 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.A = p->H1; a.lda = sh.h1; a.B = W + dl.w2; a.ldb = sh.h1; a.D = p->H2; a.ldd = sh.h2;
   a.M = sh.B; a.N = sh.h2; a.K = sh.h1; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b2 - dl.small_begin);
   a.mask_out = train ? p->m2 : nullptr; a.ldmask = p->ldm2;
+  a.bn = choose_bn(a.M, a.N, 1);
+  set_pair(a, 1);
   if (launch_gemm_kk(a) != 0) return -1;
   a = base_args(st);
   a.A = p->H2; a.lda = sh.h2; a.B = W + dl.w3; a.ldb = sh.h2; a.D = p->H3; a.ldd = sh.h3;
   a.M = sh.B; a.N = sh.h3; a.K = sh.h2; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b3 - dl.small_begin);
   a.mask_out = train ? p->m3 : nullptr; a.ldmask = p->ldm3;
+  a.bn = choose_bn(a.M, a.N, 1);
+  set_pair(a, 1);
   if (launch_gemm_kk(a) != 0) return -1;
   mark(p, st, "gemm2+gemm3");
   return 0;
@@ -488,13 +506,15 @@ static int wgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n_out, const __nv_
   a.A = dy; a.lda = n_out; a.a_mn = true; a.B = x; a.ldb = k_in; a.b_mn = true;
   a.D = reinterpret_cast<float*>(p->slab + p->sl.dense_grad) + off; a.ldd = k_in;
   a.M = n_out; a.N = k_in; a.K = p->sh.B; a.epi = EPI_F32_ATOMIC;
-  const int tiles = ((n_out + BM - 1) / BM) * ((k_in + 255) / 256);
-  int splits = num_sms() / (tiles > 0 ? tiles : 1);
+  a.bn = 256;
+  set_pair(a, 2);
+  const int ctas = a.pair ? 2 : 1;
+  const int tiles = ((n_out + BM * ctas - 1) / (BM * ctas)) * ((k_in + 255) / 256);
+  int splits = (num_sms() / ctas) / (tiles > 0 ? tiles : 1);
   const int kb = (p->sh.B + BK - 1) / BK;
   if (splits > kb) splits = kb;
   if (splits < 1) splits = 1;
   a.splits = splits;
-  a.bn = 256;
   return launch_gemm_mnmn(a);
 }
 
@@ -503,6 +523,8 @@ static int dgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n, const __nv_bflo
   GemmArgs a = base_args(st);
   a.A = dy; a.lda = n; a.B = w; a.ldb = k; a.b_mn = true; a.D = out; a.ldd = k;
   a.M = p->sh.B; a.N = k; a.K = n; a.epi = EPI_DRELU_BF16; a.mask_in = mask; a.ldmask = ldmask;
+  a.bn = choose_bn(a.M, a.N, 1);
+  set_pair(a, 3);
   return launch_gemm_kmn(a);
 }
 
@@ -645,6 +667,7 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   a.A = p->dZ1; a.lda = sh.h1; a.B = W + dl.w1; a.ldb = sh.K0; a.b_mn = true;
   a.M = sh.B; a.N = sh.F * kEmbDim; a.K = sh.h1; a.epi = EPI_PUSH_ROWS; a.row_dst = p->row_dst; a.slots = sh.F;
   a.bn = 256;
+  set_pair(a, 4);
   if (launch_gemm_kmn(a) != 0) return -1;
   mark(p, st, "dgrad1+push");
   return 0;
