@@ -9,7 +9,7 @@ N > 1 is launched by ``python -m torch.distributed.run --nproc-per-node N ... be
 (one rank per GPU).  Rank 0 prints ONE JSON line.  `value` is device-timed (CUDA events around the
 K steps, max over ranks) with inputs resident on the device; `e2e` repeats the measurement through
 the public API with a pinned-host -> device copy of every step's inputs and a device -> host read of
-the step's loss inside the timed region.  Synthetic data, random-init weights (no network).
+the step's loss inside the timed region (GraphedTrainLoop: the copies are nodes of the replayed graph).  Synthetic data, random-init weights (no network).
 """
 from __future__ import annotations
 
@@ -227,22 +227,24 @@ def main() -> int:
         host_barrier()
         dev_ms = e0.elapsed_time(e1)
         # ---------------- end-to-end region: pinned host -> device every step, loss read back -----
-        host_barrier()
-        one_step()
+        # Through the public training-loop API (models/wide_deep_loop.py): Ge steps per CUDA-graph
+        # replay, the graph holding the pinned-host -> device copies of the Ge input batches (second
+        # stream, running ahead of the compute) and the device -> host copies of the Ge losses.
+        from distributed_tensorflow_b200.models.wide_deep_loop import GraphedTrainLoop
+        Ge = next(g for g in (10, 8, 5, 4, 2, 1) if args.steps % g == 0)
+        tr.join()
         stream.synchronize()
+        loop = GraphedTrainLoop(tr, [pool_h[i % args.pool] for i in range(Ge)], stream=stream)
+        host_barrier()
+        loop.run()
+        loop.losses()
         t0 = time.perf_counter()
         e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e2.record(stream)
         last_loss = 0.0
-        for i in range(args.steps):
-            load_static(pool_h[i % args.pool])     # H2D from pinned memory
-            if graph is not None and G == 1:
-                graph.replay()
-            else:
-                tr.step(s_ids, s_dense, s_labels)  # public API call, one step per host round trip
-            loss_host.copy_(tr.last_loss_sum(), non_blocking=True)
-            stream.synchronize()                   # the caller looks at every step's loss
-            last_loss = float(loss_host[0]) / cfg.batch
+        for i in range(0, args.steps, Ge):
+            loop.run()                             # Ge steps: H2D of their inputs, compute, apply, D2H of the losses
+            last_loss = loop.losses()[-1]          # the caller looks at every step's loss (waits for the replay)
         tr.join()
         e3.record(stream)
         stream.synchronize()
@@ -274,7 +276,7 @@ def main() -> int:
                        "l2": "per-step working set (55 MB gathered operand + random rows of a 2.5 GB table + 54 MB "
                              "mailbox) exceeds the 126 MB L2; ids change every step"},
             "e2e": {"value": global_batch * args.steps / (e2e_ms / 1e3), "unit": "examples/s",
-                    "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
+                    "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4, "steps_per_graph": Ge,
                     "last_loss": last_loss},
             "gpu_launches": int(launches_per_step) * args.steps,
             "gpu_launches_per_step": int(launches_per_step),

@@ -59,6 +59,9 @@ struct GemmParams {
   int dense_cols;                     // 64
   unsigned long long* tile_flags;     // [m_tiles][kFlagWords]: 4-bit arrival counter per (row-tile, chunk), zero before launch
   unsigned int* chunk_counter;        // [1] reserved
+  // optional side gather: one fp32 per (row, slot) fetched from wide_src[m*slots+f] into wide_out
+  const unsigned long long* wide_src;
+  float* wide_out;
   unsigned long long* trace;          // debugging only (bench/pull_trace.py): globaltimer stamps, nullptr = off
   // --- fused dense pull (all-gather + GEMM): B is row-sharded over ranks; tile n reads its rows
   //     straight from the owning rank through that rank's tensor map (global memory array) ---
@@ -508,8 +511,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         m_t = m_base + rr / kSlicesPerTile;
         row0 = m_t * BM + (rr % kSlicesPerTile) * kSliceRows;
       };
-      auto issue = [&](uint4 (&v)[8], int f, int row0) {
+      auto issue = [&](uint4 (&v)[8], float& wv, int f, int row0) {
         if (f < p.slots) {
+          // the wide (linear) weight of the same 16 ids rides along: one 4-byte load per row
+          if (p.wide_src != nullptr && lane < kSliceRows && row0 + lane < p.M) {
+            const unsigned long long wa = __ldg(p.wide_src + static_cast<long long>(row0 + lane) * p.slots + f);
+            asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(wv) : "l"(wa));
+          }
           // lanes 0..15 fetch the 16 row addresses once; every step broadcasts the one it needs, so
           // the eight 16-byte row loads of a lane are issued back to back.  Rows past M and null
           // addresses read a harmless local location instead of being predicated off: a predicated
@@ -535,13 +543,15 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
       };
-      auto retire = [&](const uint4 (&v)[8], int m_t, int f, int row0) {
+      auto retire = [&](const uint4 (&v)[8], float wv, int m_t, int f, int row0) {
         unsigned long long* tr = nullptr;
         if (p.trace && lane == 0 && trace_it < 8) {
           tr = p.trace + ((static_cast<long long>(blockIdx.x) * kNumGatherWarps + gw) * 8 + trace_it) * 4;
           tr[0] = globaltimer_ns();
         }
         if (f < p.slots) {
+          if (p.wide_src != nullptr && lane < kSliceRows && row0 + lane < p.M)
+            p.wide_out[static_cast<long long>(row0 + lane) * p.slots + f] = wv;
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
             const int pc = u * 32 + lane;
@@ -573,26 +583,27 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
       if (first < total_slices) {
         uint4 va[8], vb[8];
+        float wa = 0.f, wb = 0.f;
         int ma, fa, ra, mb, fb, rb;
         long long s0 = first;
         locate(s0, ma, fa, ra);
-        issue(va, fa, ra);
+        issue(va, wa, fa, ra);
         for (;;) {
           const long long s1 = s0 + stride;
           const bool have1 = s1 < total_slices;
           if (have1) {
             locate(s1, mb, fb, rb);
-            issue(vb, fb, rb);
+            issue(vb, wb, fb, rb);
           }
-          retire(va, ma, fa, ra);
+          retire(va, wa, ma, fa, ra);
           if (!have1) break;
           s0 = s1 + stride;
           const bool have2 = s0 < total_slices;
           if (have2) {
             locate(s0, ma, fa, ra);
-            issue(va, fa, ra);
+            issue(va, wa, fa, ra);
           }
-          retire(vb, mb, fb, rb);
+          retire(vb, wb, mb, fb, rb);
           if (!have2) break;
         }
       }

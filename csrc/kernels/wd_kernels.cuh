@@ -184,7 +184,8 @@ __global__ void wd_dense_pad_kernel(const float* __restrict__ raw, __nv_bfloat16
 }
 
 // ------------------------------------------------------------------------------------------ loss
-// One warp per example: wide gather-sum over the owning shards (P2P loads), last layer h3 . w4,
+// One warp per example: sum of the wide weights (gathered from the owning shards by the fused pull
+// kernel's gather warps), last layer h3 . w4,
 // sigmoid cross-entropy, dlogit; then (training) the wide gradient is written straight into the
 // owners' mailboxes, dZ3 = dlogit * w4 masked by ReLU'(h3), and block-reduced gradients of w4 / b4 /
 // wide bias.  SURVEY.md 2E rows K5, K6.
@@ -192,7 +193,7 @@ template <bool TRAIN>
 __global__ void __launch_bounds__(256)
 wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict__ mask3, long long ldmask,
                const float* __restrict__ small, int off_w4, int off_b4, int off_wide_b,
-               const unsigned long long* __restrict__ wide_src, const unsigned long long* __restrict__ dl_dst,
+               const float* __restrict__ wide_vals, const unsigned long long* __restrict__ dl_dst,
                const float* __restrict__ labels, int B, int F, int H3, float inv_batch,
                float* __restrict__ dlogit, __nv_bfloat16* __restrict__ dz3, float* __restrict__ g_small,
                float* __restrict__ loss_acc, float* __restrict__ prob_out) {
@@ -212,12 +213,8 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
 
   for (int m = blockIdx.x * (blockDim.x >> 5) + warp; m < B; m += nwarps) {
     float wide = 0.f;
-    for (int f = lane; f < F; f += 32) {
-      const float* p = reinterpret_cast<const float*>(wide_src[static_cast<long long>(m) * F + f]);
-      float v;
-      asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(v) : "l"(p));
-      wide += v;
-    }
+    // the wide weights of this example's ids were fetched from their owners by the fused pull
+    for (int f = lane; f < F; f += 32) wide += wide_vals[static_cast<long long>(m) * F + f];
     float dot = 0.f;
     float hv[4][8];
 #pragma unroll

@@ -50,6 +50,7 @@ struct dtf_wd_plan {
   uint32_t *m1 = nullptr, *m2 = nullptr, *m3 = nullptr;
   int ldm1 = 0, ldm2 = 0, ldm3 = 0;
   unsigned long long *row_src = nullptr, *wide_src = nullptr, *row_dst = nullptr, *dl_dst = nullptr;
+  float* wide_vals = nullptr;   // [B*F] wide weights of the batch's ids, filled by the fused pull
   float* dlogit = nullptr;
   float* prob = nullptr;
   // zeroed at the start of every step: cnt[kMaxWorld] | chunk_counter | pad | loss_acc[2] | tile_flags[m_tiles][kFlagWords] (64-bit)
@@ -265,6 +266,7 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   ok &= (p->m3 = p->alloc<uint32_t>("mask3", B * p->ldm3)) != nullptr;
   ok &= (p->row_src = p->alloc<unsigned long long>("row_src", sh.cap)) != nullptr;
   ok &= (p->wide_src = p->alloc<unsigned long long>("wide_src", sh.cap)) != nullptr;
+  ok &= (p->wide_vals = p->alloc<float>("wide_vals", sh.cap)) != nullptr;
   ok &= (p->row_dst = p->alloc<unsigned long long>("row_dst", sh.cap)) != nullptr;
   ok &= (p->dl_dst = p->alloc<unsigned long long>("dl_dst", sh.cap)) != nullptr;
   ok &= (p->dlogit = p->alloc<float>("dlogit", B)) != nullptr;
@@ -450,6 +452,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.mask_out = train ? p->m1 : nullptr; a.ldmask = p->ldm1;
   a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
   a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
+  a.wide_src = p->wide_src; a.wide_out = p->wide_vals;
   a.bn = 256;
   set_pair(a, 0);
   if (launch_gemm_gather(a) != 0) return -1;
@@ -486,11 +489,11 @@ static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, boo
   if (train) {
     const size_t smem = 8 * (sh.h3 + 2) * sizeof(float);
     DTF_CUDA_OK(launch_kernel(true, wd_loss_kernel<true>, dim3(grid), dim3(256), smem, st, p->H3, p->m3,
-                              static_cast<long long>(p->ldm3), small, off_w4, off_b4, off_wb, p->wide_src, p->dl_dst, labels,
+                              static_cast<long long>(p->ldm3), small, off_w4, off_b4, off_wb, p->wide_vals, p->dl_dst, labels,
                               sh.B, sh.F, sh.h3, inv_batch, p->dlogit, p->dZ3, g_small, p->loss_acc,
                               static_cast<float*>(nullptr)));
   } else {
-    wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_src, nullptr,
+    wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_vals, nullptr,
                                                 nullptr, sh.B, sh.F, sh.h3, 0.f, nullptr, nullptr, nullptr, nullptr,
                                                 p->prob);
   }

@@ -335,9 +335,9 @@ class WideDeepTrainer:
             _lib.check(self._L.dtf_wd_broadcast_dense(self._h, self._stream()), "dtf_wd_broadcast_dense")
             torch.cuda.synchronize(self.device)
         if step is not None:
-            self.step_offset = int(step) - self.global_step()
+            self.set_global_step(int(step))
 
-    step_offset = 0
+    step_offset = 0   # kept for callers that add it; the device counter itself is restored now
 
     def export_config(self) -> dict:
         d = asdict(self.cfg)
@@ -366,8 +366,16 @@ class WideDeepTrainer:
         return self._loss_views[int(self._L.dtf_wd_last_parity(self._h)) if not self.cfg.sync else 0]
 
     def global_step(self) -> int:
-        self._L.dtf_wd_info(self._h, C.byref(self.info))
-        return int(self.info.step)
+        """Number of applies this shard has performed -- read from the device-resident step state, so
+        it also counts steps executed by CUDA-graph replays (synchronises the device)."""
+        torch.cuda.synchronize(self.device)
+        return int(self.buffer("step_state", torch.int64)[0].item())
+
+    def set_global_step(self, step: int) -> None:
+        """Restore path: also the ``t`` of Adam's bias correction."""
+        torch.cuda.synchronize(self.device)
+        self.buffer("step_state", torch.int64)[0:1].fill_(int(step))
+        torch.cuda.synchronize(self.device)
 
     def close(self) -> None:
         if self._h:

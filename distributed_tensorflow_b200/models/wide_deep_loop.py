@@ -1,0 +1,95 @@
+"""Graph-replayed training loop for the wide-and-deep trainer.
+
+The reference's worker loop feeds one example per ``sess.run`` through ``feed_dict``
+(/root/reference/trainer/task.py:232-246): every step pays a host round trip.  Here ``G`` consecutive
+steps are captured once into a CUDA graph *together with* the host->device copies of their input
+batches (from pinned host buffers, on a second stream so that they run ahead of the compute) and the
+device->host copies of the per-step losses; one ``run()`` then costs one graph launch for ``G`` steps.
+
+    loop = GraphedTrainLoop(trainer, host_batches)      # G = len(host_batches) pinned (ids, dense, labels)
+    for _ in range(n):
+        # (refill host_batches[i] in place here: they are read again by the next run)
+        loop.run()
+        losses = loop.losses()                          # G mean losses, waits for the replay
+
+In async mode the ps-side applies of step t overlap the compute of step t+1 inside the graph
+(:meth:`WideDeepTrainer.step` with ``overlap=True``); the graph ends with a join, so replays are
+self-contained.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from .wide_deep import WideDeepTrainer
+
+HostBatch = Tuple[torch.Tensor, torch.Tensor, torch.Tensor]
+
+
+class GraphedTrainLoop:
+    def __init__(self, trainer: WideDeepTrainer, host_batches: Sequence[HostBatch],
+                 stream: Optional[torch.cuda.Stream] = None, warmup: int = 3):
+        if not host_batches:
+            raise ValueError("GraphedTrainLoop needs at least one host batch")
+        cfg = trainer.cfg
+        for ids, dense, labels in host_batches:
+            if not (ids.is_pinned() and dense.is_pinned() and labels.is_pinned()):
+                raise ValueError("host batches must live in pinned memory (tensor.pin_memory())")
+            if tuple(ids.shape) != (cfg.batch, cfg.slots) or ids.dtype != torch.int32:
+                raise ValueError("ids must be int32 [batch, slots]")
+            if tuple(dense.shape) != (cfg.batch, cfg.dense_in) or dense.dtype != torch.float32:
+                raise ValueError("dense must be float32 [batch, dense_in]")
+            if tuple(labels.shape) != (cfg.batch,) or labels.dtype != torch.float32:
+                raise ValueError("labels must be float32 [batch]")
+        self.trainer = trainer
+        self.host_batches = list(host_batches)
+        self.steps_per_run = len(self.host_batches)
+        dev = trainer.device
+        # high priority: the compute kernels get the SMs first, the overlapped applies fill the rest
+        self.stream = stream or torch.cuda.Stream(device=dev, priority=-1)
+        self._copy_stream = torch.cuda.Stream(device=dev)
+        self._dev = [tuple(torch.empty_like(t, device=dev) for t in b) for b in self.host_batches]
+        self._loss_host = torch.zeros(self.steps_per_run).pin_memory()
+        self._done = torch.cuda.Event()
+        self.h2d_bytes_per_step = sum(t.numel() * t.element_size() for t in self.host_batches[0])
+        self.d2h_bytes_per_step = 4
+        with torch.cuda.stream(self.stream):
+            for i in range(max(1, warmup)):     # lazy initialisation (streams, kernels) before capture
+                b = self.host_batches[i % self.steps_per_run]
+                for dst, src in zip(self._dev[0], b):
+                    dst.copy_(src, non_blocking=True)
+                trainer.step(*self._dev[0])
+            trainer.join()
+            self.stream.synchronize()
+            trainer.overlap_reset()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph, stream=self.stream):
+                self._copy_stream.wait_stream(self.stream)
+                ready: List[torch.cuda.Event] = []
+                with torch.cuda.stream(self._copy_stream):
+                    for gi, b in enumerate(self.host_batches):
+                        for dst, src in zip(self._dev[gi], b):
+                            dst.copy_(src, non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(self._copy_stream)
+                        ready.append(ev)
+                for gi in range(self.steps_per_run):
+                    self.stream.wait_event(ready[gi])
+                    trainer.step(*self._dev[gi])
+                    self._loss_host[gi:gi + 1].copy_(trainer.last_loss_sum(), non_blocking=True)
+                trainer.join()
+                self.stream.wait_stream(self._copy_stream)
+            trainer.overlap_reset()
+        self.warmup_steps = max(1, warmup)
+
+    def run(self) -> None:
+        """Launch ``steps_per_run`` training steps (asynchronous; see :meth:`losses`)."""
+        with torch.cuda.stream(self.stream):
+            self.graph.replay()
+            self._done.record(self.stream)
+
+    def losses(self) -> List[float]:
+        """Mean loss of every step of the last :meth:`run` (waits for it)."""
+        self._done.synchronize()
+        return (self._loss_host / self.trainer.cfg.batch).tolist()

@@ -222,3 +222,37 @@ def test_async_serial_and_overlapped_paths_both_train_and_sync_refuses_overlap()
     t.step(*b)                                             # the plain path still works
     torch.cuda.synchronize()
     t.close()
+
+
+@pytest.mark.parametrize("sync", [False, True])
+def test_graphed_train_loop_trains_from_pinned_host_batches(sync):
+    from distributed_tensorflow_b200.models.wide_deep_loop import GraphedTrainLoop
+    cfg = _cfg(sync=sync, emb_rows=2000, lr=0.1)
+    t = _make(cfg, 1)[0]
+    g = torch.Generator().manual_seed(11)
+    w_true = torch.randn(cfg.dense_in, generator=g)
+    G = 4
+    host = []
+    for _ in range(G):
+        ids = torch.randint(0, cfg.emb_rows, (cfg.batch, cfg.slots), generator=g, dtype=torch.int32).pin_memory()
+        dense = torch.randn(cfg.batch, cfg.dense_in, generator=g).pin_memory()
+        labels = ((dense @ w_true) > 0).float().pin_memory()
+        host.append((ids, dense, labels))
+    with pytest.raises(ValueError, match="pinned"):
+        GraphedTrainLoop(t, [(host[0][0].clone(), host[0][1], host[0][2])])
+    loop = GraphedTrainLoop(t, host, warmup=2)
+    step0 = t.global_step()
+    first = None
+    for r in range(12):
+        for ids, dense, labels in host:            # refill the pinned buffers in place between replays
+            ids.copy_(torch.randint(0, cfg.emb_rows, ids.shape, generator=g, dtype=torch.int32))
+            dense.copy_(torch.randn(dense.shape, generator=g))
+            labels.copy_(((dense @ w_true) > 0).float())
+        loop.run()
+        ls = loop.losses()
+        assert len(ls) == G and all(l == l and l > 0 for l in ls)
+        first = first or ls[0]
+    assert ls[-1] < 0.7 * first, (first, ls)
+    assert t.global_step() == step0 + 12 * G
+    assert loop.h2d_bytes_per_step == cfg.batch * (cfg.slots * 4 + cfg.dense_in * 4 + 4)
+    t.close()
