@@ -30,6 +30,7 @@ struct GemmArgs {
   // fused push
   const unsigned long long* row_dst;
   bool pdl;   // launch with programmatic stream serialization (step executor)
+  int max_ctas = 0;    // cap on the persistent grid (0 = all SMs): lets two GEMMs share the GPU side by side
   bool pair = false;   // CTA pairs (cta_group::2, 256 x BN tiles); BN = 256 or 128 only
   cudaStream_t stream;
 };
@@ -90,7 +91,10 @@ int launch_gemm_t(const GemmArgs& a) {
   p.row_dst = a.row_dst;
   p.b_maps = a.b_maps; p.b_rows_per_shard = a.b_rows_per_shard;
   const int tiles = ((p.m_tiles + CTAS - 1) / CTAS) * p.n_tiles * p.splits * CTAS;   // in CTAs
-  const int sms = num_sms() / CTAS * CTAS;
+  int sms = num_sms();
+  if (a.max_ctas > 0 && a.max_ctas < sms && !GATHER) sms = a.max_ctas;
+  sms = sms / CTAS * CTAS;
+  if (sms < CTAS) sms = CTAS;
   int grid = tiles < sms ? tiles : sms;
   if (GATHER && grid < sms) grid = sms;  // gather warps of CTAs without tiles still pull rows
   const int threads = GATHER ? kNumMainThreads + kNumGatherThreads : kNumMainThreads;

@@ -71,6 +71,10 @@ struct dtf_wd_plan {
   unsigned int* zero_par[2] = {nullptr, nullptr};
   long long n_compute = 0, n_apply = 0;
   cudaEvent_t ev_push[2] = {nullptr, nullptr}, ev_apply[2] = {nullptr, nullptr};
+  // side stream: the NVLink-bound fused push runs on `push_ctas` SMs next to wgrad-1 on the others
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  int push_ctas = 0;
   bool ev_apply_valid[2] = {false, false};
   int last_compute_parity = 0;
   int apply_blocks_per_sm = 8;   // lowered while the apply shares the SMs with the next step's GEMMs
@@ -285,6 +289,16 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   for (int i = 0; i < 2; ++i) {
     cudaEventCreateWithFlags(&p->ev_push[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&p->ev_apply[i], cudaEventDisableTiming);
+    if (i == 0) {
+      int lo = 0, hi = 0;
+      cudaDeviceGetStreamPriorityRange(&lo, &hi);
+      cudaStreamCreateWithPriority(&p->side, cudaStreamNonBlocking, hi);
+      cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
+      // measured (bench.py, async): 2 GPUs 0.424 -> 0.409 ms with 48 SMs, 8 GPUs 0.473 -> 0.449 ms with 56
+      const char* e = getenv("DTF_SPLIT_PUSH");
+      p->push_ctas = e ? atoi(e) : (cfg->world > 1 ? 56 : 0);
+    }
   }
   return p;
 }
@@ -296,6 +310,9 @@ void dtf_wd_destroy(dtf_wd_plan* p) {
     if (p->ev_push[i]) cudaEventDestroy(p->ev_push[i]);
     if (p->ev_apply[i]) cudaEventDestroy(p->ev_apply[i]);
   }
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->side) cudaStreamDestroy(p->side);
   for (void* m : p->opened) dtf_symm_close_handle(m);
   for (void* q : p->owned) cudaFree(q);
   if (p->slab && p->owns_slab) dtf_symm_free(p->slab);
@@ -503,7 +520,7 @@ static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, boo
 }
 
 static int wgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n_out, const __nv_bfloat16* x, int k_in, long long off,
-                 cudaStream_t st) {
+                 cudaStream_t st, int max_ctas = 0) {
   // dW[n_out, k_in] += dy^T x, reduction over the batch; partial tiles are added by TMA reduce
   GemmArgs a = base_args(st);
   a.A = dy; a.lda = n_out; a.a_mn = true; a.B = x; a.ldb = k_in; a.b_mn = true;
@@ -513,7 +530,9 @@ static int wgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n_out, const __nv_
   set_pair(a, 2);
   const int ctas = a.pair ? 2 : 1;
   const int tiles = ((n_out + BM * ctas - 1) / (BM * ctas)) * ((k_in + 255) / 256);
-  int splits = (num_sms() / ctas) / (tiles > 0 ? tiles : 1);
+  a.max_ctas = max_ctas;
+  const int sms = (max_ctas > 0 && max_ctas < num_sms()) ? max_ctas : num_sms();
+  int splits = (sms / ctas) / (tiles > 0 ? tiles : 1);
   const int kb = (p->sh.B + BK - 1) / BK;
   if (splits > kb) splits = kb;
   if (splits < 1) splits = 1;
@@ -659,19 +678,35 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   mark(p, st, "wgrad2");
   if (dgrad(p, p->dZ2, sh.h2, W + dl.w2, sh.h1, p->m1, p->ldm1, p->dZ1, st) != 0) return -1;
   mark(p, st, "dgrad2");
-  if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st) != 0) return -1;
-  mark(p, st, "wgrad1");
-  if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
-  if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
-  if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
-  mark(p, st, "colsum x3");
   // fused push: dA = dZ1 W1[:, :F*128]; every 128-wide row goes to its owner's mailbox
   GemmArgs a = base_args(st);
   a.A = p->dZ1; a.lda = sh.h1; a.B = W + dl.w1; a.ldb = sh.K0; a.b_mn = true;
   a.M = sh.B; a.N = sh.F * kEmbDim; a.K = sh.h1; a.epi = EPI_PUSH_ROWS; a.row_dst = p->row_dst; a.slots = sh.F;
   a.bn = 256;
   set_pair(a, 4);
-  if (launch_gemm_kmn(a) != 0) return -1;
+  const bool split = p->push_ctas > 0 && p->push_ctas < num_sms() && !p->profile;
+  if (split) {
+    // wgrad-1 (tensor-bound) and the push (NVLink-bound once the shards are remote) only depend on
+    // dZ1: run them side by side, the push on `push_ctas` SMs of a second stream
+    DTF_CUDA_OK(cudaEventRecord(p->ev_fork, st));
+    DTF_CUDA_OK(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    a.stream = p->side;
+    a.max_ctas = p->push_ctas;
+    a.pdl = false;
+    if (launch_gemm_kmn(a) != 0) return -1;
+    DTF_CUDA_OK(cudaEventRecord(p->ev_join, p->side));
+  }
+  if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st, split ? num_sms() - p->push_ctas : 0) != 0) return -1;
+  mark(p, st, "wgrad1");
+  if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
+  if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
+  if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
+  mark(p, st, "colsum x3");
+  if (split) {
+    DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_join, 0));
+  } else {
+    if (launch_gemm_kmn(a) != 0) return -1;
+  }
   mark(p, st, "dgrad1+push");
   return 0;
 }
