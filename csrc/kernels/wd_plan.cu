@@ -558,51 +558,64 @@ static int colsum(const __nv_bfloat16* x, int M, int N, float* out, cudaStream_t
   return 0;
 }
 
+// which == 1: tick + sparse (embedding + wide) apply; which == 2: dense apply; 3: both
 template <int OPT>
-static int apply_t(dtf_wd_plan* p, cudaStream_t st) {
+static int apply_t(dtf_wd_plan* p, cudaStream_t st, int which = 3) {
   const SlabLayout& sl = p->sl;
-  MailboxView mv{};
-  mv.payload = reinterpret_cast<const __nv_bfloat16*>(p->slab + sl.mbx_payload);
-  mv.rows = reinterpret_cast<const int*>(p->slab + sl.mbx_rows);
-  mv.dl = reinterpret_cast<const float*>(p->slab + sl.mbx_dl);
-  mv.count = reinterpret_cast<const unsigned int*>(p->slab + sl.mbx_count);
-  mv.cap = p->sh.cap;
-  mv.world = p->cfg.world;
   const StepState* oc = p->state;
-  wd_tick_kernel<<<1, 1, 0, st>>>(p->state, p->cfg.lr, p->cfg.optimizer);
-  count_launch();
-  __nv_bfloat16* work = reinterpret_cast<__nv_bfloat16*>(p->slab + sl.emb_bf16);
-  float* wide = reinterpret_cast<float*>(p->slab + sl.wide);
-  int grid = num_sms() * 8;
-  if (p->apply_blocks_per_sm != 8) {
-    // overlapped with the next step's compute: many short-lived blocks (one pair of entries per warp)
-    // instead of a persistent grid, so that SMs are handed to the higher-priority GEMM CTAs as soon
-    // as those become runnable and the apply fills whatever room they leave
-    const long long want = (p->sh.cap + 15) / 16;
-    grid = static_cast<int>(want > grid ? want : grid);
-  }
-  if (p->cfg.sync) {
-    wd_sparse_count_kernel<<<num_sms() * 4, 256, 0, st>>>(mv, p->row_state);
-    mark(p, st, "sparse count");
-    wd_sparse_apply_sync_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->row_state, p->G, p->wide_G, p->emb_master, p->emb_s1,
-                                                           p->emb_s2, work, wide, p->wide_s1, p->wide_s2, oc);
-    count_launch(2);
-    mark(p, st, "sparse apply (sync)");
-  } else {
-    wd_sparse_apply_entries_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
-                                                              p->wide_s1, p->wide_s2, oc);
+  if (which & 1) {
+    MailboxView mv{};
+    mv.payload = reinterpret_cast<const __nv_bfloat16*>(p->slab + sl.mbx_payload);
+    mv.rows = reinterpret_cast<const int*>(p->slab + sl.mbx_rows);
+    mv.dl = reinterpret_cast<const float*>(p->slab + sl.mbx_dl);
+    mv.count = reinterpret_cast<const unsigned int*>(p->slab + sl.mbx_count);
+    mv.cap = p->sh.cap;
+    mv.world = p->cfg.world;
+    wd_tick_kernel<<<1, 1, 0, st>>>(p->state, p->cfg.lr, p->cfg.optimizer);
     count_launch();
-    mark(p, st, "sparse apply entries");
+    __nv_bfloat16* work = reinterpret_cast<__nv_bfloat16*>(p->slab + sl.emb_bf16);
+    float* wide = reinterpret_cast<float*>(p->slab + sl.wide);
+    int grid = num_sms() * 8;
+    if (p->apply_blocks_per_sm != 8) {
+      // overlapped with the next step's compute: many short-lived blocks (one pair of entries per warp)
+      // instead of a persistent grid, so that SMs are handed to the higher-priority GEMM CTAs as soon
+      // as those become runnable and the apply fills whatever room they leave
+      const long long want = (p->sh.cap + 15) / 16;
+      grid = static_cast<int>(want > grid ? want : grid);
+    }
+    if (p->cfg.sync) {
+      wd_sparse_count_kernel<<<num_sms() * 4, 256, 0, st>>>(mv, p->row_state);
+      mark(p, st, "sparse count");
+      wd_sparse_apply_sync_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->row_state, p->G, p->wide_G, p->emb_master, p->emb_s1,
+                                                             p->emb_s2, work, wide, p->wide_s1, p->wide_s2, oc);
+      count_launch(2);
+      mark(p, st, "sparse apply (sync)");
+    } else {
+      wd_sparse_apply_entries_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
+                                                                p->wide_s1, p->wide_s2, oc);
+      count_launch();
+      mark(p, st, "sparse apply entries");
+    }
   }
-  const long long dense_n4 = (p->dense_hi - p->dense_lo) / 4;
-  const int dense_grid = p->apply_blocks_per_sm != 8 ? static_cast<int>((dense_n4 + 255) / 256) : num_sms() * 4;
-  wd_dense_apply_kernel<OPT><<<dense_grid, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
-                                                            p->dense_master, p->dense_s1, p->dense_s2, oc,
-                                                            p->dl.small_begin);
-  count_launch();
-  mark(p, st, "dense apply");
+  if (which & 2) {
+    const long long dense_n4 = (p->dense_hi - p->dense_lo) / 4;
+    const int dense_grid = p->apply_blocks_per_sm != 8 ? static_cast<int>((dense_n4 + 255) / 256) : num_sms() * 4;
+    wd_dense_apply_kernel<OPT><<<dense_grid, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
+                                                              p->dense_master, p->dense_s1, p->dense_s2, oc,
+                                                              p->dl.small_begin);
+    count_launch();
+    mark(p, st, "dense apply");
+  }
   DTF_CUDA_OK(cudaGetLastError());
   return 0;
+}
+
+static int apply_dispatch(dtf_wd_plan* p, cudaStream_t st, int which) {
+  switch (p->cfg.optimizer) {
+    case WD_SGD: return apply_t<WD_SGD>(p, st, which);
+    case WD_ADAGRAD: return apply_t<WD_ADAGRAD>(p, st, which);
+    default: return apply_t<WD_ADAM>(p, st, which);
+  }
 }
 
 extern "C" {
@@ -655,8 +668,12 @@ int dtf_wd_profile_read_abs(dtf_wd_plan* p, char* buf, size_t cap) {
 
 // forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
 // [B*dense_in], labels f32 [B]
-int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, void* stream_) {
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas);
+
+// defer_wgrad: leave out the weight / bias gradient kernels (the caller runs weight_grads() on another
+// stream) and keep only the chain the sparse push depends on
+static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, cudaStream_t st,
+                        bool defer_wgrad) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   const int par = p->cfg.sync ? 0 : static_cast<int>(p->n_compute & 1);
@@ -670,12 +687,16 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   mark(p, st, "loss+wide");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
-  if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
-  mark(p, st, "wgrad3");
+  if (!defer_wgrad) {
+    if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
+    mark(p, st, "wgrad3");
+  }
   if (dgrad(p, p->dZ3, sh.h3, W + dl.w3, sh.h2, p->m2, p->ldm2, p->dZ2, st) != 0) return -1;
   mark(p, st, "dgrad3");
-  if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
-  mark(p, st, "wgrad2");
+  if (!defer_wgrad) {
+    if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
+    mark(p, st, "wgrad2");
+  }
   if (dgrad(p, p->dZ2, sh.h2, W + dl.w2, sh.h1, p->m1, p->ldm1, p->dZ1, st) != 0) return -1;
   mark(p, st, "dgrad2");
   // fused push: dA = dZ1 W1[:, :F*128]; every 128-wide row goes to its owner's mailbox
@@ -684,6 +705,11 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   a.M = sh.B; a.N = sh.F * kEmbDim; a.K = sh.h1; a.epi = EPI_PUSH_ROWS; a.row_dst = p->row_dst; a.slots = sh.F;
   a.bn = 256;
   set_pair(a, 4);
+  if (defer_wgrad) {
+    if (launch_gemm_kmn(a) != 0) return -1;
+    mark(p, st, "dgrad1+push");
+    return 0;
+  }
   const bool split = p->push_ctas > 0 && p->push_ctas < num_sms() && !p->profile;
   if (split) {
     // wgrad-1 (tensor-bound) and the push (NVLink-bound once the shards are remote) only depend on
@@ -696,12 +722,8 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
     if (launch_gemm_kmn(a) != 0) return -1;
     DTF_CUDA_OK(cudaEventRecord(p->ev_join, p->side));
   }
-  if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st, split ? num_sms() - p->push_ctas : 0) != 0) return -1;
-  mark(p, st, "wgrad1");
-  if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
-  if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
-  if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
-  mark(p, st, "colsum x3");
+  (void)grad;
+  if (weight_grads(p, st, split ? num_sms() - p->push_ctas : 0) != 0) return -1;
   if (split) {
     DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_join, 0));
   } else {
@@ -709,6 +731,34 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   }
   mark(p, st, "dgrad1+push");
   return 0;
+}
+
+// dW1 and the three bias gradients (plus dW2, dW3 when they were deferred)
+static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st) {
+  const WdShapes& sh = p->sh;
+  const DenseLayout& dl = p->dl;
+  if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
+  if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
+  return weight_grads(p, st, 0);
+}
+
+static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
+  const WdShapes& sh = p->sh;
+  const DenseLayout& dl = p->dl;
+  float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
+  if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st, wgrad1_ctas) != 0) return -1;
+  mark(p, st, "wgrad1");
+  if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
+  if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
+  if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
+  mark(p, st, "colsum x3");
+  return 0;
+}
+
+// forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
+// [B*dense_in], labels f32 [B]
+int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, void* stream_) {
+  return compute_impl(p, ids, dense_raw, labels, reinterpret_cast<cudaStream_t>(stream_), false);
 }
 
 // cross-rank barrier on the device (no-op publish for a single rank)
@@ -733,12 +783,7 @@ int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
 int dtf_wd_step_apply(dtf_wd_plan* p, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   select_parity(p, p->cfg.sync ? 0 : static_cast<int>(p->n_apply & 1));
-  int rc;
-  switch (p->cfg.optimizer) {
-    case WD_SGD: rc = apply_t<WD_SGD>(p, st); break;
-    case WD_ADAGRAD: rc = apply_t<WD_ADAGRAD>(p, st); break;
-    default: rc = apply_t<WD_ADAM>(p, st); break;
-  }
+  const int rc = apply_dispatch(p, st, 3);
   if (rc == 0) {
     p->step += 1;
     p->n_apply += 1;
@@ -746,7 +791,43 @@ int dtf_wd_step_apply(dtf_wd_plan* p, void* stream_) {
   return rc;
 }
 
+// Sync-replica step.  The sparse push only depends on the dgrad chain, so the weight / bias gradient
+// kernels (tensor-bound, ~115 us) are taken off the critical path: they run on the side stream while
+// the main stream does barrier + sparse apply (HBM-bound, ~160 us); the dense apply waits for both
+// (and, across ranks, for one more barrier).  DTF_SYNC_PIPE=0 restores the serial order.
+static bool sync_pipe() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DTF_SYNC_PIPE");
+    v = (e == nullptr || e[0] != '0') ? 1 : 0;
+  }
+  return v == 1;
+}
+
 int dtf_wd_step(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  if (p->cfg.sync && sync_pipe() && !p->profile) {
+    if (compute_impl(p, ids, dense_raw, labels, st, true) != 0) return -1;
+    DTF_CUDA_OK(cudaEventRecord(p->ev_fork, st));
+    DTF_CUDA_OK(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    if (weight_grads_deferred(p, p->side) != 0) return -1;
+    DTF_CUDA_OK(cudaEventRecord(p->ev_join, p->side));
+    if (dtf_wd_barrier(p, 1, stream_) != 0) return -1;          // every sparse push has landed
+    select_parity(p, 0);
+    // short-lived apply blocks (as in the async overlap): a persistent apply grid would hold every
+    // thread slot until it ends and keep the next weight-gradient kernel's CTAs off the SMs
+    p->apply_blocks_per_sm = p->cfg.overlap_apply_blocks > 0 ? p->cfg.overlap_apply_blocks : 2;
+    const int rc_sparse = apply_dispatch(p, st, 1);
+    p->apply_blocks_per_sm = 8;
+    if (rc_sparse != 0) return -1;
+    DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_join, 0));
+    if (p->cfg.world > 1 && dtf_wd_barrier(p, 0, stream_) != 0) return -1;   // every rank's dense gradient is complete
+    if (apply_dispatch(p, st, 2) != 0) return -1;
+    p->step += 1;
+    p->n_apply += 1;
+    if (p->cfg.world > 1 && dtf_wd_barrier(p, 0, stream_) != 0) return -1;   // updated shards visible to all
+    return 0;
+  }
   if (dtf_wd_step_compute(p, ids, dense_raw, labels, stream_) != 0) return -1;
   if (dtf_wd_barrier(p, 1, stream_) != 0) return -1;   // every push and gradient has landed
   if (dtf_wd_step_apply(p, stream_) != 0) return -1;
