@@ -127,3 +127,16 @@ def linear_dw(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None
     epi = EPI_F32_ATOMIC if accumulate else EPI_F32
     # GEMM view: D[N, K] = (dy^T)[N, M] * (x^T)[K, M]^T ; both stored with the reduction dim as rows
     return gemm_raw(dy, 1, x, 1, out, N, K, M, epi, splits=splits, bn=bn)
+
+
+def set_pair_mode(on: bool) -> None:
+    """CTA-pair tiles (``tcgen05.mma.cta_group::2``: the two SMs of a TPC share one 256 x BN tile) for
+    every GEMM launch that has a pair instantiation; off = single-CTA 128 x BN tiles everywhere.
+    Process-wide; the initial value comes from ``DTF_PAIR`` (default on)."""
+    L = _lib.lib()
+    L.dtf_gemm_set_pair_mode.restype = None
+    L.dtf_gemm_set_pair_mode(ctypes.c_int(int(bool(on))))
+
+
+def pair_mode() -> bool:
+    return bool(_lib.lib().dtf_gemm_get_pair_mode())

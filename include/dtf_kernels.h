@@ -52,11 +52,22 @@ int dtf_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long lo
                   const void* mask_in, void* mask_out, long long ldmask, int splits, int bn,
                   void* stream);
 
+/* CTA-pair tiles: GEMMs with a pair instantiation run as clusters of two CTAs (the two SMs of a TPC)
+ * that share one 256 x BN tile through tcgen05.mma.cta_group::2.  Process-wide switch; initial value
+ * from the environment variable DTF_PAIR (default 1). */
+void dtf_gemm_set_pair_mode(int on);
+int dtf_gemm_get_pair_mode(void);
+
+/* Debugging: device buffer (>= 71000 x 8 bytes, zeroed by the caller) that receives %globaltimer stamps
+ * of the gather warps and TMA producers of the following fused-pull launches (bench/pull_trace.py);
+ * NULL switches the stamps off. */
+void dtf_debug_set_pull_trace(void* buf);
+
 /* Fused parameter pull: H[M,N] = act([gather(row_src) | dense_x] * W^T + bias).  row_src[m*slots+f]
  * is the device address (local or peer-mapped) of the 128-wide bf16 embedding row of example m,
  * slot f; gather warps of the same persistent kernel fetch rows over NVLink while its tcgen05
  * warps multiply row-tiles that already arrived.  The gathered operand stays in a_buf
- * [M, slots*128 + dense_cols].  scratch: dtf_pull_gemm_scratch_bytes(M) bytes of device memory
+ * [M, slots*128 + dense_cols] (slots <= 63).  scratch: dtf_pull_gemm_scratch_bytes(M) bytes of device memory
  * owned by the caller (cleared by the call).  Replaces the ps->worker variable read (RecvTensor)
  * plus the first Mul of reference trainer/task.py:137. */
 size_t dtf_pull_gemm_scratch_bytes(int M);

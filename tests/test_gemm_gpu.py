@@ -138,3 +138,53 @@ def test_allgather_gemm_over_peer_memory():
     y = F.allgather_gemm(x, [w0, (w1.data_ptr(), rows)], b, relu=False)
     ref = x.float() @ torch.cat([w0, w1.to("cuda:0")]).float().t()
     assert _rel(y, ref) < 1e-2
+
+
+def test_cta_pair_tiles_match_single_cta_tiles():
+    """Every layout / epilogue with a cta_group::2 instantiation: same numbers as the single-CTA
+    kernels, including an odd number of 128-row tiles (last pair half empty) and ragged N / K."""
+    from distributed_tensorflow_b200.ops import fused as F
+    from distributed_tensorflow_b200.ops import gemm as G
+    torch.manual_seed(5)
+    before = G.pair_mode()
+    try:
+        for M, N, K in [(256, 256, 128), (640, 512, 200), (1100, 1024, 1024), (2048, 296, 520)]:
+            x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+            w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+            b = torch.randn(N, device="cuda")
+            dy = (torch.randn(M, N, device="cuda") * 0.5).bfloat16()
+            keep = torch.rand(M, K, device="cuda") > 0.5
+            got = {}
+            for mode in (False, True):
+                G.set_pair_mode(mode)
+                assert G.pair_mode() == mode
+                m = torch.zeros(M, G.mask_words(N), dtype=torch.int32, device="cuda")
+                got[mode] = (G.linear_fw(x, w, b, relu=True, bn=256, mask_out=m), m,
+                             G.linear_fw(x, w, None, out_dtype=torch.float32, bn=256),
+                             G.linear_dx(dy, w, G.pack_mask(keep), bn=256),
+                             G.linear_dw(dy, x, splits=0), G.linear_dw(dy, x, splits=3))
+            for a, c in zip(got[False], got[True]):
+                if a.dtype == torch.int32:
+                    assert torch.equal(a, c)
+                else:
+                    assert _rel(c, a) < 2e-3
+            assert _rel(got[True][0], torch.relu(x.float() @ w.float().t() + b)) < 1e-2
+            assert _rel(got[True][4], dy.float().t() @ x.float()) < 1e-4
+        # fused pull and push on pairs
+        M, slots, N = 1000, 6, 512
+        table = (torch.randn(5000, 128, device="cuda") * 0.1).bfloat16()
+        ids = torch.randint(0, 5000, (M, slots), device="cuda")
+        dense = torch.randn(M, 64, device="cuda").bfloat16()
+        w = (torch.randn(N, slots * 128 + 64, device="cuda") * 0.05).bfloat16()
+        b = torch.randn(N, device="cuda")
+        outs = {}
+        for mode in (False, True):
+            G.set_pair_mode(mode)
+            H, a = F.pull_gemm(F.row_addresses(table, ids), dense, w, b, relu=True)
+            outs[mode] = (H.clone(), a.clone())
+        assert torch.equal(outs[True][1], outs[False][1])
+        assert _rel(outs[True][0], outs[False][0]) < 2e-3
+        ref_a = torch.cat([table[ids.view(-1)].view(M, slots * 128), dense], dim=1)
+        assert torch.equal(outs[True][1], ref_a)
+    finally:
+        G.set_pair_mode(before)
