@@ -73,6 +73,15 @@ def run(name, table):
     print("  producer waits (row-tile: wait start -> end us): " +
           " ".join("%d:%.0f->%.0f" % (int(mt[i]), float(wstart[i]), float(wend[i])) for i in order[:: max(1, len(order) // 24)]))
     print("  last producer wait ends at %.1f us" % float(wend.max()), flush=True)
+    mma = (pr[:, :, 2] - t00)[pu] / 1e3
+    ep = (t[70272:70272 + 148 * 8].view(148, 8) - t00)[pu] / 1e3
+    for k in range(int(pu.sum(1).max())):
+        u = pu[:, k]
+        print("    GEMM wave %d: MMAs done p10 %.1f p50 %.1f max %.1f | epilogue issued p50 %.1f max %.1f" % (
+            k, pct(((pr[:, k, 2] - t00)[u]) / 1e3, 0.1), pct(((pr[:, k, 2] - t00)[u]) / 1e3, 0.5),
+            float(((pr[:, k, 2] - t00)[u]).max()) / 1e3,
+            pct((t[70272:70272 + 148 * 8].view(148, 8)[:, k] - t00)[u] / 1e3, 0.5),
+            float((t[70272:70272 + 148 * 8].view(148, 8)[:, k] - t00)[u].max()) / 1e3), flush=True)
 
 
 local = torch.empty(rows, 128, device="cuda:0", dtype=torch.bfloat16).normal_(0, 0.05)

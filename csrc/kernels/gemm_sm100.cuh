@@ -341,6 +341,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
       mbar_wait(tfull_bar(buf), (it >> 1) & 1);
       tc_fence_after();
+      if constexpr (GATHER) {
+        if (p.trace && warp == 2 && lane == 0) p.trace[65536 + (blockIdx.x * 8 + it) * 4 + 2] = globaltimer_ns();   // MMAs of the tile done
+      }
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN;
 #pragma unroll 1
       for (int c = 0; c < BN / CW; ++c) {
@@ -435,6 +438,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (lane == 0) {
         if constexpr (kPair) mbar_arrive_cluster(mapa_shared(tempty_bar(buf), 0));
         else mbar_arrive(tempty_bar(buf));
+      }
+      if constexpr (GATHER) {
+        if (p.trace && warp == 2 && lane == 0) p.trace[70272 + blockIdx.x * 8 + it] = globaltimer_ns();   // epilogue of the tile issued
       }
     }
     tma_store_wait_all();

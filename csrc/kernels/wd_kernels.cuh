@@ -138,11 +138,18 @@ __global__ void wd_dense_broadcast_kernel(const float* __restrict__ master, long
 __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V, PeerTable pt, SlabLayout sl,
                                 long long cap, unsigned int* __restrict__ cnt,
                                 unsigned long long* __restrict__ row_src, unsigned long long* __restrict__ wide_src,
-                                unsigned long long* __restrict__ row_dst, unsigned long long* __restrict__ dl_dst) {
+                                unsigned long long* __restrict__ row_dst, unsigned long long* __restrict__ dl_dst,
+                                const float* __restrict__ dense_raw, __nv_bfloat16* __restrict__ dense_out, int B,
+                                int dense_in, int dense_pad) {
   __shared__ unsigned int s_cnt[kMaxWorld];
   __shared__ unsigned int s_base[kMaxWorld];
   pdl_launch_dependents();
   pdl_wait();
+  // rides along: the dense features as zero-padded bf16 (the last chunk of the GEMM-1 operand)
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B * dense_pad; i += gridDim.x * blockDim.x) {
+    const int m = i / dense_pad, c = i % dense_pad;
+    dense_out[i] = __float2bfloat16(c < dense_in ? dense_raw[m * dense_in + c] : 0.f);
+  }
   if (threadIdx.x < kMaxWorld) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -169,17 +176,6 @@ __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V,
     row_dst[e] = reinterpret_cast<unsigned long long>(oslab + sl.mbx_payload) + entry * (kEmbDim * 2);
     dl_dst[e] = reinterpret_cast<unsigned long long>(oslab + sl.mbx_dl) + entry * 4;
     reinterpret_cast<int*>(oslab + sl.mbx_rows)[entry] = static_cast<int>(lrow);
-  }
-}
-
-__global__ void wd_dense_pad_kernel(const float* __restrict__ raw, __nv_bfloat16* __restrict__ out, int B, int dense_in,
-                                    int dense_pad) {
-  pdl_launch_dependents();
-  pdl_wait();
-  const int n = B * dense_pad;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int m = i / dense_pad, c = i % dense_pad;
-    out[i] = __float2bfloat16(c < dense_in ? raw[m * dense_in + c] : 0.f);
   }
 }
 
@@ -296,45 +292,60 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------ colsum
-// out[n] += sum_m x[m, n]  (bias gradients).  Block = 256 columns x `rows_per_block` rows; every
-// thread streams 8 columns (one 16-byte load per row) for one of 8 row groups.
+// out[n] += sum_m x[m, n]  (bias gradients) for up to three matrices in one launch.  A block covers
+// 256 columns x `rows_per_block` rows of one matrix; every thread streams 8 columns (one 16-byte load
+// per row) for one of 8 row groups.
+struct ColsumJobs {
+  const __nv_bfloat16* x[3];
+  float* out[3];
+  int N[3];
+  int block_end[3];   // exclusive prefix sums of the blocks per job
+  int M;
+  int rows_per_block;
+};
+
 __global__ void __launch_bounds__(256)
-wd_colsum_kernel(const __nv_bfloat16* __restrict__ x, int M, int N, long long ld, int rows_per_block,
-                 float* __restrict__ out) {
-  __shared__ float s[8][256];
+wd_colsum_kernel(ColsumJobs jobs) {
+  __shared__ float s[8][256 + 8];
   pdl_launch_dependents();
   pdl_wait();
+  int j = 0;
+  while (j < 2 && static_cast<int>(blockIdx.x) >= jobs.block_end[j]) ++j;
+  const int local = blockIdx.x - (j == 0 ? 0 : jobs.block_end[j - 1]);
+  const int N = jobs.N[j], M = jobs.M;
+  const long long ld = N;
+  const __nv_bfloat16* __restrict__ x = jobs.x[j];
+  const int col_blocks = (N + 255) / 256;
+  const int bx = local % col_blocks, by = local / col_blocks;
   const int cg = threadIdx.x & 31, rg = threadIdx.x >> 5;
-  const int col = blockIdx.x * 256 + cg * 8;
-  const int r0 = blockIdx.y * rows_per_block;
-  const int r1 = min(M, r0 + rows_per_block);
+  const int col = bx * 256 + cg * 8;
+  const int r0 = by * jobs.rows_per_block, r1 = min(M, r0 + jobs.rows_per_block);
   float acc[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int q = 0; q < 8; ++q) acc[q] = 0.f;
   if (col + 8 <= N) {
-#pragma unroll 4
     for (int r = r0 + rg; r < r1; r += 8) {
-      const uint4 raw = ld_global_nc_v4(x + static_cast<long long>(r) * ld + col);
+      const uint4 raw = *reinterpret_cast<const uint4*>(x + static_cast<long long>(r) * ld + col);
       const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 f = __bfloat1622float2(h[j]);
-        acc[2 * j] += f.x;
-        acc[2 * j + 1] += f.y;
+      for (int q = 0; q < 4; ++q) {
+        const float2 f = __bfloat1622float2(h[q]);
+        acc[2 * q] += f.x;
+        acc[2 * q + 1] += f.y;
       }
     }
-  } else if (col < N) {
+  } else {
     for (int r = r0 + rg; r < r1; r += 8)
-      for (int j = 0; j < 8 && col + j < N; ++j) acc[j] += __bfloat162float(x[static_cast<long long>(r) * ld + col + j]);
+      for (int q = 0; q < 8 && col + q < N; ++q) acc[q] += __bfloat162float(x[static_cast<long long>(r) * ld + col + q]);
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) s[rg][cg * 8 + j] = acc[j];
+  for (int q = 0; q < 8; ++q) s[rg][cg * 8 + q] = acc[q];
   __syncthreads();
   float t = 0.f;
 #pragma unroll
   for (int w = 0; w < 8; ++w) t += s[w][threadIdx.x];
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c < N) atomicAdd(out + c, t);
+  const int c = bx * 256 + threadIdx.x;
+  if (c < N) atomicAdd(jobs.out[j] + c, t);
 }
 
 // ------------------------------------------------------------------------------------------ sparse

@@ -102,19 +102,22 @@ struct dtf_wd_plan {
 
 // zero fill by kernel instead of cudaMemsetAsync: memset nodes on IPC-exported (peer-mapped) memory
 // made CUDA-graph replays of the multi-rank step slow
-__global__ void wd_zero_kernel(uint4* __restrict__ p, size_t n16) {
+__global__ void wd_zero_kernel(uint4* __restrict__ p, size_t n16, uint4* __restrict__ q, size_t m16) {
   pdl_launch_dependents();
   pdl_wait();
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n16;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x)
-    p[i] = make_uint4(0, 0, 0, 0);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  for (size_t i = t; i < n16; i += stride) p[i] = make_uint4(0, 0, 0, 0);
+  for (size_t i = t; i < m16; i += stride) q[i] = make_uint4(0, 0, 0, 0);
 }
-static int zero_fill(void* ptr, size_t bytes, cudaStream_t st) {
-  const size_t n16 = (bytes + 15) / 16;
-  int grid = static_cast<int>((n16 + 255) / 256);
+// zero one or two regions with one launch
+static int zero_fill(void* ptr, size_t bytes, cudaStream_t st, void* ptr2 = nullptr, size_t bytes2 = 0) {
+  const size_t n16 = (bytes + 15) / 16, m16 = (bytes2 + 15) / 16;
+  int grid = static_cast<int>(((n16 > m16 ? n16 : m16) + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   if (grid < 1) grid = 1;
-  DTF_CUDA_OK(launch_kernel(true, wd_zero_kernel, dim3(grid), dim3(256), 0, st, static_cast<uint4*>(ptr), n16));
+  DTF_CUDA_OK(launch_kernel(true, wd_zero_kernel, dim3(grid), dim3(256), 0, st, static_cast<uint4*>(ptr), n16,
+                            static_cast<uint4*>(ptr2), m16));
   count_launch();
   return 0;
 }
@@ -448,17 +451,17 @@ static GemmArgs base_args(cudaStream_t st) {
   return a;
 }
 
-static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaStream_t st, bool train) {
+static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaStream_t st, bool train,
+                   bool scratch_zeroed = false) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   const int n = sh.B * sh.F;
   mark(p, st, "begin");
-  if (zero_fill(p->zero_region, p->zero_bytes, st) != 0) return -1;
+  if (!scratch_zeroed && zero_fill(p->zero_region, p->zero_bytes, st) != 0) return -1;
   DTF_CUDA_OK(launch_kernel(true, wd_route_kernel, dim3((n + 255) / 256), dim3(256), 0, st, ids, n, sh.V, p->pt, p->sl,
-                            sh.cap, p->cnt, p->row_src, p->wide_src, p->row_dst, p->dl_dst));
-  DTF_CUDA_OK(launch_kernel(true, wd_dense_pad_kernel, dim3((sh.B * sh.dense_pad + 255) / 256), dim3(256), 0, st,
-                            dense_raw, p->dense_x, sh.B, sh.dense_in, sh.dense_pad));
-  count_launch(2);
+                            sh.cap, p->cnt, p->row_src, p->wide_src, p->row_dst, p->dl_dst, dense_raw, p->dense_x, sh.B,
+                            sh.dense_in, sh.dense_pad));
+  count_launch();
   mark(p, st, "route+pad");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
@@ -501,7 +504,8 @@ static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, boo
   const int off_w4 = static_cast<int>(dl.w4 - dl.small_begin), off_b4 = static_cast<int>(dl.b4 - dl.small_begin),
             off_wb = static_cast<int>(dl.wide_b - dl.small_begin);
   const float inv_batch = 1.0f / (static_cast<float>(sh.B) * (p->cfg.sync ? p->cfg.world : 1));
-  int grid = num_sms() * 2;
+  static const int loss_mult = getenv("DTF_LOSS_GRID") ? atoi(getenv("DTF_LOSS_GRID")) : 2;
+  int grid = num_sms() * loss_mult;
   if (grid > (sh.B + 7) / 8) grid = (sh.B + 7) / 8;
   if (train) {
     const size_t smem = 8 * (sh.h3 + 2) * sizeof(float);
@@ -550,10 +554,23 @@ static int dgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n, const __nv_bflo
   return launch_gemm_kmn(a);
 }
 
-static int colsum(const __nv_bfloat16* x, int M, int N, float* out, cudaStream_t st) {
-  const int rpb = 128;
-  dim3 grid((N + 255) / 256, (M + rpb - 1) / rpb);
-  DTF_CUDA_OK(launch_kernel(true, wd_colsum_kernel, grid, dim3(256), 0, st, x, M, N, static_cast<long long>(N), rpb, out));
+// bias gradients of the three hidden layers in one launch
+static int colsum3(const __nv_bfloat16* x0, int n0, float* o0, const __nv_bfloat16* x1, int n1, float* o1,
+                   const __nv_bfloat16* x2, int n2, float* o2, int M, cudaStream_t st) {
+  ColsumJobs j{};
+  j.M = M;
+  j.rows_per_block = 64;
+  const int row_blocks = (M + j.rows_per_block - 1) / j.rows_per_block;
+  const __nv_bfloat16* xs[3] = {x0, x1, x2};
+  float* os[3] = {o0, o1, o2};
+  const int ns[3] = {n0, n1, n2};
+  int total = 0;
+  for (int i = 0; i < 3; ++i) {
+    j.x[i] = xs[i]; j.out[i] = os[i]; j.N[i] = ns[i];
+    total += ((ns[i] + 255) / 256) * row_blocks;
+    j.block_end[i] = total;
+  }
+  DTF_CUDA_OK(launch_kernel(true, wd_colsum_kernel, dim3(total), dim3(256), 0, st, j));
   count_launch();
   return 0;
 }
@@ -681,8 +698,10 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   p->last_compute_parity = par;
   p->n_compute += 1;
   mark(p, st, "step");
-  if (zero_fill(p->slab + p->sl.dense_grad, static_cast<size_t>(p->P_pad) * 4, st) != 0) return -1;
-  if (forward(p, ids, dense_raw, st, true) != 0) return -1;
+  // one launch clears the dense-gradient buffer and the per-step scratch (counters, loss, arrival flags)
+  if (zero_fill(p->slab + p->sl.dense_grad, static_cast<size_t>(p->P_pad) * 4, st, p->zero_region, p->zero_bytes) != 0)
+    return -1;
+  if (forward(p, ids, dense_raw, st, true, true) != 0) return -1;
   if (launch_loss(p, labels, st, true) != 0) return -1;
   mark(p, st, "loss+wide");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
@@ -748,9 +767,7 @@ static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
   if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st, wgrad1_ctas) != 0) return -1;
   mark(p, st, "wgrad1");
-  if (colsum(p->dZ1, sh.B, sh.h1, grad + dl.b1, st) != 0) return -1;
-  if (colsum(p->dZ2, sh.B, sh.h2, grad + dl.b2, st) != 0) return -1;
-  if (colsum(p->dZ3, sh.B, sh.h3, grad + dl.b3, st) != 0) return -1;
+  if (colsum3(p->dZ1, sh.h1, grad + dl.b1, p->dZ2, sh.h2, grad + dl.b2, p->dZ3, sh.h3, grad + dl.b3, sh.B, st) != 0) return -1;
   mark(p, st, "colsum x3");
   return 0;
 }
