@@ -536,10 +536,20 @@ static int wgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n_out, const __nv_
   const int tiles = ((n_out + BM * ctas - 1) / (BM * ctas)) * ((k_in + 255) / 256);
   a.max_ctas = max_ctas;
   const int sms = (max_ctas > 0 && max_ctas < num_sms()) ? max_ctas : num_sms();
-  int splits = (sms / ctas) / (tiles > 0 ? tiles : 1);
+  // split-K factor: fewest k-blocks on the critical path, counting whole waves of the persistent grid
+  // plus ~2 k-blocks' worth of epilogue (fp32 TMA reduce-add of the partial tile) per wave
+  const int units = sms / ctas > 0 ? sms / ctas : 1;
   const int kb = (p->sh.B + BK - 1) / BK;
-  if (splits > kb) splits = kb;
-  if (splits < 1) splits = 1;
+  int splits = 1;
+  long long best = -1;
+  for (int sp = 1; sp <= 16 && sp <= kb; ++sp) {
+    const long long waves = (static_cast<long long>(tiles) * sp + units - 1) / units;
+    const long long cost = waves * ((kb + sp - 1) / sp + 2);
+    if (best < 0 || cost < best) {
+      best = cost;
+      splits = sp;
+    }
+  }
   a.splits = splits;
   return launch_gemm_mnmn(a);
 }
