@@ -32,7 +32,16 @@ struct Drv {
   CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
   CUresult (*Export)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long) = nullptr;
   CUresult (*Import)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType) = nullptr;
+  // multicast objects (NVLS): optional, mc_ok says whether the entry points exist
+  CUresult (*McCreate)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*) = nullptr;
+  CUresult (*McAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
+  CUresult (*McBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t,
+                        unsigned long long) = nullptr;
+  CUresult (*McGetGranularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags) = nullptr;
+  CUresult (*DeviceGet)(CUdevice*, int) = nullptr;
+  CUresult (*DeviceGetAttribute)(int*, CUdevice_attribute, CUdevice) = nullptr;
   bool ok = false;
+  bool mc_ok = false;
 };
 
 template <typename T>
@@ -56,6 +65,9 @@ Drv& drv() {
            load("cuMemAddressFree", &d.AddressFree) && load("cuMemMap", &d.Map) && load("cuMemUnmap", &d.Unmap) &&
            load("cuMemSetAccess", &d.SetAccess) && load("cuMemExportToShareableHandle", &d.Export) &&
            load("cuMemImportFromShareableHandle", &d.Import);
+    d.mc_ok = d.ok && load("cuMulticastCreate", &d.McCreate) && load("cuMulticastAddDevice", &d.McAddDevice) &&
+              load("cuMulticastBindMem", &d.McBindMem) && load("cuMulticastGetGranularity", &d.McGetGranularity) &&
+              load("cuDeviceGet", &d.DeviceGet) && load("cuDeviceGetAttribute", &d.DeviceGetAttribute);
   });
   return d;
 }
@@ -224,6 +236,168 @@ int dtf_symm_import_fd(int fd, size_t size, void** out_ptr) {
   std::lock_guard<std::mutex> l(g_mu);
   g_maps[p] = Mapping{h, size, true, true};
   *out_ptr = p;
+  return 0;
+}
+
+// ---- multicast objects (NVLS: in-switch reduction and broadcast) ---------------------------------
+// One multicast object spans the same byte range of every rank's slab.  A multimem.ld_reduce on its
+// mapping returns the sum of all ranks' values (reduced inside NVSwitch), a multimem.st writes all
+// ranks' copies with one store.  Life cycle (all ranks, with host barriers between the phases):
+// rank 0 creates the object and passes its file descriptor around; every rank adds its device; every
+// rank binds the leading `bytes` of its slab and maps the object.
+namespace {
+struct McObject {
+  CUmemGenericAllocationHandle handle = 0;
+  size_t bytes = 0;
+};
+std::map<long long, McObject> g_mc;
+long long g_mc_next = 1;
+
+CUmulticastObjectProp mc_prop(int num_devices, size_t bytes) {
+  CUmulticastObjectProp prop{};
+  prop.numDevices = static_cast<unsigned int>(num_devices);
+  prop.size = bytes;
+  prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  prop.flags = 0;
+  return prop;
+}
+}  // namespace
+
+// 1 when the current device and driver support multicast objects
+int dtf_mc_supported(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  (void)cudaFree(nullptr);
+  Drv& d = drv();
+  if (!d.mc_ok) return 0;
+  CUdevice cd;
+  int v = 0;
+  if (d.DeviceGet(&cd, dev) != CUDA_SUCCESS) return 0;
+  if (d.DeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, cd) != CUDA_SUCCESS) return 0;
+  return v ? 1 : 0;
+}
+
+// largest multiple of the multicast granularity that fits into `bytes` (0: unsupported)
+long long dtf_mc_usable_bytes(int num_devices, size_t bytes) {
+  Drv& d = drv();
+  if (!d.mc_ok) return 0;
+  CUmulticastObjectProp prop = mc_prop(num_devices, bytes);
+  size_t gran = 0;
+  if (d.McGetGranularity(&gran, &prop, CU_MULTICAST_GRANULARITY_MINIMUM) != CUDA_SUCCESS || gran == 0) return 0;
+  return static_cast<long long>(bytes / gran * gran);
+}
+
+// rank 0: create the object (bytes from dtf_mc_usable_bytes) and export it as a file descriptor
+int dtf_mc_create(int num_devices, size_t bytes, long long* id_out, int* fd_out) {
+  Drv& d = drv();
+  if (!d.mc_ok) {
+    set_error("multicast: driver entry points unavailable");
+    return -1;
+  }
+  CUmulticastObjectProp prop = mc_prop(num_devices, bytes);
+  CUmemGenericAllocationHandle h = 0;
+  CUresult r = d.McCreate(&h, &prop);
+  if (r != CUDA_SUCCESS) {
+    set_error("multicast: cuMulticastCreate(%d devices, %zu bytes) failed (%d)", num_devices, bytes, (int)r);
+    return -1;
+  }
+  int fd = -1;
+  r = d.Export(&fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+  if (r != CUDA_SUCCESS) {
+    d.Release(h);
+    set_error("multicast: export of the object failed (%d)", (int)r);
+    return -1;
+  }
+  std::lock_guard<std::mutex> l(g_mu);
+  const long long id = g_mc_next++;
+  g_mc[id] = McObject{h, bytes};
+  *id_out = id;
+  *fd_out = fd;
+  return 0;
+}
+
+int dtf_mc_import(int fd, size_t bytes, long long* id_out) {
+  Drv& d = drv();
+  if (!d.mc_ok) {
+    set_error("multicast: driver entry points unavailable");
+    return -1;
+  }
+  (void)cudaFree(nullptr);
+  CUmemGenericAllocationHandle h = 0;
+  const CUresult r = d.Import(&h, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+  if (r != CUDA_SUCCESS) {
+    set_error("multicast: import of the object failed (%d)", (int)r);
+    return -1;
+  }
+  std::lock_guard<std::mutex> l(g_mu);
+  const long long id = g_mc_next++;
+  g_mc[id] = McObject{h, bytes};
+  *id_out = id;
+  return 0;
+}
+
+int dtf_mc_add_device(long long id) {
+  Drv& d = drv();
+  McObject o;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    auto it = g_mc.find(id);
+    if (it == g_mc.end()) {
+      set_error("multicast: unknown object %lld", id);
+      return -2;
+    }
+    o = it->second;
+  }
+  int dev = 0;
+  DTF_CUDA_OK(cudaGetDevice(&dev));
+  CUdevice cd;
+  if (d.DeviceGet(&cd, dev) != CUDA_SUCCESS) {
+    set_error("multicast: cuDeviceGet(%d) failed", dev);
+    return -1;
+  }
+  const CUresult r = d.McAddDevice(o.handle, cd);
+  if (r != CUDA_SUCCESS) {
+    set_error("multicast: cuMulticastAddDevice(device %d) failed (%d)", dev, (int)r);
+    return -1;
+  }
+  return 0;
+}
+
+// after every rank has added its device: bind the leading bytes of `slab` (a dtf_symm_alloc VMM
+// allocation) and map the object; *mc_ptr_out addresses all ranks' copies at once
+int dtf_mc_bind_map(long long id, void* slab, void** mc_ptr_out) {
+  Drv& d = drv();
+  McObject o;
+  Mapping m;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    auto it = g_mc.find(id);
+    auto im = g_maps.find(slab);
+    if (it == g_mc.end() || im == g_maps.end() || !im->second.vmm || im->second.imported) {
+      set_error("multicast: unknown object or %p is not a local VMM slab", slab);
+      return -2;
+    }
+    o = it->second;
+    m = im->second;
+  }
+  if (o.bytes > m.size) {
+    set_error("multicast: object (%zu bytes) larger than the slab mapping (%zu)", o.bytes, m.size);
+    return -2;
+  }
+  int dev = 0;
+  DTF_CUDA_OK(cudaGetDevice(&dev));
+  CUresult r = d.McBindMem(o.handle, 0, m.handle, 0, o.bytes, 0);
+  if (r != CUDA_SUCCESS) {
+    set_error("multicast: cuMulticastBindMem(%zu bytes) failed (%d)", o.bytes, (int)r);
+    return -1;
+  }
+  void* p = nullptr;
+  if (map_handle(o.handle, o.bytes, dev, &p) != 0) return -1;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    g_maps[p] = Mapping{o.handle, o.bytes, true, true};
+  }
+  *mc_ptr_out = p;
   return 0;
 }
 

@@ -580,7 +580,10 @@ template <int OPT>
 __global__ void __launch_bounds__(256)
 wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, int sum_first,
                       float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2,
-                      const StepState* __restrict__ stp, long long small_begin) {
+                      const StepState* __restrict__ stp, long long small_begin, uint8_t* __restrict__ mc) {
+  // mc != nullptr: multicast mapping of the slabs (NVLS).  The sum over the replicas' gradients is
+  // then one multimem.ld_reduce (added inside NVSwitch) instead of `world` peer loads, and the new
+  // values reach every rank's working copy with one multimem.st instead of `world` peer stores.
   // sum_first = 1 (sync-replica): one optimizer step on the sum of all replicas' gradients.
   // sum_first = 0 (async / Hogwild): every replica's gradient is applied on its own, in rank order,
   //   exactly as if each had been sent separately; all of them are read up front so that the
@@ -591,18 +594,29 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
        q += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long i = lo + q * 4;
     float4 g[kMaxWorld];
+    float4 gsum = make_float4(0, 0, 0, 0);
+    const bool use_mc_sum = mc != nullptr && sum_first;
+    if (use_mc_sum) {
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(gsum.x), "=f"(gsum.y), "=f"(gsum.z), "=f"(gsum.w)
+                   : "l"(mc + sl.dense_grad + i * 4)
+                   : "memory");
+    } else {
 #pragma unroll
-    for (int r = 0; r < kMaxWorld; ++r)
-      if (r < pt.world) g[r] = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < pt.world) g[r] = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
+    }
     float4 w = *reinterpret_cast<float4*>(master + (i - lo));
     float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
     if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + (i - lo));
     if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + (i - lo));
     if (sum_first) {
-      float4 t = make_float4(0, 0, 0, 0);
+      float4 t = gsum;
+      if (!use_mc_sum) {
 #pragma unroll
-      for (int r = 0; r < kMaxWorld; ++r)
-        if (r < pt.world) { t.x += g[r].x; t.y += g[r].y; t.z += g[r].z; t.w += g[r].w; }
+        for (int r = 0; r < kMaxWorld; ++r)
+          if (r < pt.world) { t.x += g[r].x; t.y += g[r].y; t.z += g[r].z; t.w += g[r].w; }
+      }
       opt_update<OPT>(w.x, t.x, a.x, v.x, oc);
       opt_update<OPT>(w.y, t.y, a.y, v.y, oc);
       opt_update<OPT>(w.z, t.z, a.z, v.z, oc);
@@ -623,9 +637,20 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
     uint2 pk;
     pk.x = pack_bf16x2(w.x, w.y);
     pk.y = pack_bf16x2(w.z, w.w);
-    for (int r = 0; r < pt.world; ++r) {
-      *reinterpret_cast<uint2*>(pt.slab[r] + sl.wbf16 + i * 2) = pk;
-      if (i >= small_begin) *reinterpret_cast<float4*>(pt.slab[r] + sl.small_f32 + (i - small_begin) * 4) = w;
+    if (mc != nullptr) {
+      asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc + sl.wbf16 + i * 2),
+                   "f"(__uint_as_float(pk.x)), "f"(__uint_as_float(pk.y))
+                   : "memory");
+      if (i >= small_begin)
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + sl.small_f32 +
+                                                                                            (i - small_begin) * 4),
+                     "f"(w.x), "f"(w.y), "f"(w.z), "f"(w.w)
+                     : "memory");
+    } else {
+      for (int r = 0; r < pt.world; ++r) {
+        *reinterpret_cast<uint2*>(pt.slab[r] + sl.wbf16 + i * 2) = pk;
+        if (i >= small_begin) *reinterpret_cast<float4*>(pt.slab[r] + sl.small_f32 + (i - small_begin) * 4) = w;
+      }
     }
   }
 }

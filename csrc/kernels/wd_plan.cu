@@ -75,6 +75,7 @@ struct dtf_wd_plan {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int push_ctas = 0;
+  uint8_t* mc = nullptr;   // multicast (NVLS) mapping of all ranks' slabs, nullptr = plain peer loads / stores
   bool ev_apply_valid[2] = {false, false};
   int last_compute_parity = 0;
   int apply_blocks_per_sm = 8;   // lowered while the apply shares the SMs with the next step's GEMMs
@@ -348,6 +349,28 @@ int dtf_wd_info(dtf_wd_plan* p, dtf_wd_info_t* out) {
   out->small_begin = p->dl.small_begin;
   out->slab_bytes = static_cast<long long>(p->sl.total);
   out->step = p->step;
+  return 0;
+}
+
+// Hand the plan a multicast mapping of the first `bytes` of every rank's slab (dtf_mc_bind_map).  The
+// dense-parameter apply then reduces the replicas' gradients with multimem.ld_reduce and broadcasts
+// the new weights with multimem.st.  Refused when the regions it would address lie beyond `bytes`.
+int dtf_wd_attach_multicast(dtf_wd_plan* p, void* mc_ptr, long long bytes) {
+  if (mc_ptr == nullptr) {
+    p->mc = nullptr;
+    return 0;
+  }
+  for (int par = 0; par < 2; ++par) {
+    const SlabLayout& sl = p->sl_par[par];
+    const long long need_grad = static_cast<long long>(sl.dense_grad) + p->P_pad * 4;
+    const long long need_w = static_cast<long long>(sl.wbf16) + p->P_pad * 2;
+    const long long need_small = static_cast<long long>(sl.small_f32) + (p->P_pad - p->dl.small_begin) * 4;
+    if (need_grad > bytes || need_w > bytes || need_small > bytes) {
+      set_error("dtf_wd_attach_multicast: mapping of %lld bytes does not cover the dense regions", bytes);
+      return -2;
+    }
+  }
+  p->mc = static_cast<uint8_t*>(mc_ptr);
   return 0;
 }
 
@@ -629,7 +652,7 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st, int which = 3) {
     const int dense_grid = p->apply_blocks_per_sm != 8 ? static_cast<int>((dense_n4 + 255) / 256) : num_sms() * 4;
     wd_dense_apply_kernel<OPT><<<dense_grid, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
                                                               p->dense_master, p->dense_s1, p->dense_s2, oc,
-                                                              p->dl.small_begin);
+                                                              p->dl.small_begin, p->mc);
     count_launch();
     mark(p, st, "dense apply");
   }

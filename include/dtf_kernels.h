@@ -123,6 +123,17 @@ int dtf_symm_open_handle(const void* handle, void** out_ptr); /* maps a peer's s
 int dtf_symm_close_handle(void* ptr);
 int dtf_symm_enable_peer(int peer_device);                    /* same-process peers */
 
+/* Multicast objects (NVLS): one object spans the same leading byte range of every rank's slab; on its
+ * mapping multimem.ld_reduce returns the sum over all ranks (reduced inside NVSwitch) and multimem.st
+ * writes every rank's copy.  Collective life cycle with host barriers between the phases: rank 0
+ * dtf_mc_create + passes the fd; others dtf_mc_import; all dtf_mc_add_device; all dtf_mc_bind_map. */
+int dtf_mc_supported(void);
+long long dtf_mc_usable_bytes(int num_devices, size_t bytes);
+int dtf_mc_create(int num_devices, size_t bytes, long long* id_out, int* fd_out);
+int dtf_mc_import(int fd, size_t bytes, long long* id_out);
+int dtf_mc_add_device(long long id);
+int dtf_mc_bind_map(long long id, void* slab, void** mc_ptr_out);
+
 /* ---- wide-and-deep plan: the training / serving step executor -------------------------------- *
  * Every rank is a worker and a parameter-server shard at once (embedding row r on rank
  * r % world, dense parameters range-partitioned), the B200 mapping of the ps / worker / master
@@ -166,6 +177,7 @@ void* dtf_wd_slab_ptr(dtf_wd_plan*);
 int dtf_wd_slab_is_vmm(dtf_wd_plan*);
 int dtf_wd_slab_fd(dtf_wd_plan*, int* fd_out);
 int dtf_wd_attach_fds(dtf_wd_plan*, const int* fds /* world descriptors, own entry ignored */);
+int dtf_wd_attach_multicast(dtf_wd_plan*, void* mc_ptr, long long bytes);   /* NVLS path of the dense apply; NULL = off */
 int dtf_wd_attach_ipc(dtf_wd_plan*, const void* handles /* world * handle_size bytes; legacy, slow mappings */);
 int dtf_wd_attach_ptrs(dtf_wd_plan*, void* const* slabs /* world pointers */);
 int dtf_wd_init_params(dtf_wd_plan*, unsigned long long seed, void* stream);
