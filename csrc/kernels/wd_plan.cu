@@ -3,6 +3,7 @@
 // call so that Python is not on the critical path.  It plays the part of TensorFlow's C++
 // master/worker executor behind sess.run(train_op) in the reference (reference
 // trainer/task.py:236).
+#include <nvtx3/nvToolsExt.h>
 #include <math.h>
 #include <string.h>
 
@@ -123,7 +124,28 @@ static int zero_fill(void* ptr, size_t bytes, cudaStream_t st, void* ptr2 = null
   return 0;
 }
 
+// NVTX (DTF_NVTX=1): one range per executor call and a marker at the end of every kernel group, so that
+// a timeline tool shows pull / MLP / loss / backward / push / apply without per-kernel name matching.
+static bool nvtx_on() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DTF_NVTX");
+    v = (e != nullptr && e[0] == '1') ? 1 : 0;
+  }
+  return v == 1;
+}
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name) : on(nvtx_on()) {
+    if (on) nvtxRangePushA(name);
+  }
+  ~NvtxRange() {
+    if (on) nvtxRangePop();
+  }
+};
+
 static void mark(dtf_wd_plan* p, cudaStream_t st, const char* name) {
+  if (nvtx_on()) nvtxMarkA(name);
   if (!p->profile) return;
   cudaEvent_t e;
   cudaEventCreate(&e);
@@ -661,6 +683,7 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st, int which = 3) {
 }
 
 static int apply_dispatch(dtf_wd_plan* p, cudaStream_t st, int which) {
+  NvtxRange nvtx_range(which == 1 ? "wd_apply_sparse" : (which == 2 ? "wd_apply_dense" : "wd_apply"));
   switch (p->cfg.optimizer) {
     case WD_SGD: return apply_t<WD_SGD>(p, st, which);
     case WD_ADAGRAD: return apply_t<WD_ADAGRAD>(p, st, which);
@@ -724,6 +747,7 @@ static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas);
 // stream) and keep only the chain the sparse push depends on
 static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, const float* labels, cudaStream_t st,
                         bool defer_wgrad) {
+  NvtxRange nvtx_range("wd_step_compute");
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   const int par = p->cfg.sync ? 0 : static_cast<int>(p->n_compute & 1);

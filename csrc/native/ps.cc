@@ -191,6 +191,20 @@ static const float kAdadeltaRho = 0.95f, kAdadeltaEps = 1e-8f;
 static const float kRmsDecay = 0.9f, kRmsMomentum = 0.0f, kRmsEps = 1e-10f;
 static const float kFtrlPower = -0.5f, kFtrlL1 = 0.f, kFtrlL2 = 0.f;
 
+// The three places where variable storage is touched without a lock, by design (Hogwild, TF's
+// use_locking=False).  They are separate non-inlined functions so that csrc/native/tsan.supp can name
+// exactly these and ThreadSanitizer keeps checking everything else.
+__attribute__((noinline)) static void copy_value_unlocked(Writer& w, const Var* v) { w.bytes(v->data.data(), v->data.size()); }
+__attribute__((noinline)) static std::vector<char> snapshot_value_unlocked(const Var* v) { return v->data; }
+__attribute__((noinline)) static void hogwild_read_beta_powers(Store* st, float* b1p, float* b2p) {
+  *b1p = st->slot("beta1_power", nullptr, kAdamB1)->f()[0];
+  *b2p = st->slot("beta2_power", nullptr, kAdamB2)->f()[0];
+}
+__attribute__((noinline)) static void hogwild_advance_beta_powers(Store* st) {
+  st->find("beta1_power")->f()[0] *= kAdamB1;
+  st->find("beta2_power")->f()[0] *= kAdamB2;
+}
+
 static int apply_one(Store* st, const std::string& name, int opt, float lr, const float* g, size_t n,
                      float b1p, float b2p) {
   Var* v = st->find(name);
@@ -285,7 +299,7 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       if (!r.ok) return -1;
       Var* v = store.find(name);
       if (!v) return -10;
-      w.bytes(v->data.data(), v->data.size());
+      copy_value_unlocked(w, v);
       return 0;
     }
     case OP_LIST: {
@@ -318,15 +332,13 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       if (!r.ok) return -1;
       float b1p = kAdamB1, b2p = kAdamB2;
       if (opt == DTFN_OPT_ADAM) {
-        b1p = store.slot("beta1_power", nullptr, kAdamB1)->f()[0];
-        b2p = store.slot("beta2_power", nullptr, kAdamB2)->f()[0];
+        hogwild_read_beta_powers(&store, &b1p, &b2p);
       }
       std::vector<float> grad(n / 4);
       memcpy(grad.data(), g, grad.size() * 4);
       const int rc = apply_one(&store, name, opt, lr, grad.data(), grad.size(), b1p, b2p);
       if (rc == 0 && opt == DTFN_OPT_ADAM) {
-        store.find("beta1_power")->f()[0] *= kAdamB1;
-        store.find("beta2_power")->f()[0] *= kAdamB2;
+        hogwild_advance_beta_powers(&store);
       }
       return rc;
     }
@@ -336,8 +348,7 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       const float lr = r.f32();
       float b1p = kAdamB1, b2p = kAdamB2;
       if (opt == DTFN_OPT_ADAM && k > 0) {
-        b1p = store.slot("beta1_power", nullptr, kAdamB1)->f()[0];
-        b2p = store.slot("beta2_power", nullptr, kAdamB2)->f()[0];
+        hogwild_read_beta_powers(&store, &b1p, &b2p);
       }
       std::vector<std::string> names;
       for (int i = 0; i < k && r.ok; ++i) {
@@ -351,8 +362,7 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
         if (rc != 0) return rc;
       }
       if (opt == DTFN_OPT_ADAM && k > 0) {
-        store.find("beta1_power")->f()[0] *= kAdamB1;
-        store.find("beta2_power")->f()[0] *= kAdamB2;
+        hogwild_advance_beta_powers(&store);
       }
       const std::string step_name = r.str();
       const int64_t inc = r.i64();
@@ -377,12 +387,12 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       if (want) {
         for (const std::string& nm : names) {
           Var* v = store.find(nm);
-          w.bytes(v->data.data(), v->data.size());
+          copy_value_unlocked(w, v);
         }
         for (const std::string& nm : extra) {
           Var* v = store.find(nm);
           if (!v) return -10;
-          w.bytes(v->data.data(), v->data.size());
+          copy_value_unlocked(w, v);
         }
       }
       return 0;
@@ -455,7 +465,7 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
         if (std::find(excl.begin(), excl.end(), kv.first) != excl.end()) continue;
         // snapshot without stopping writers: like TF, a checkpoint taken during Hogwild training is
         // not an atomic cut across variables
-        std::vector<char> copy = kv.second->data;
+        std::vector<char> copy = snapshot_value_unlocked(kv.second.get());
         if (dtfn_bundle_writer_add(bw, kv.first.c_str(), kv.second->dtype, static_cast<int>(kv.second->dims.size()),
                                    kv.second->dims.data(), copy.data(), copy.size()) != 0) {
           dtfn_bundle_writer_abandon(bw);

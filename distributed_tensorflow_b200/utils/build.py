@@ -94,7 +94,7 @@ def build_kernels(force: bool = False, jobs: int | None = None, verbose: bool = 
 
 def build_native(force: bool = False, jobs: int | None = None) -> Path:
     """Compile csrc/native/*.cc -> _lib/libdtf_native.so (CPU runtime)."""
-    srcs = sorted((CSRC / "native").glob("*.cc"))
+    srcs = [p for p in sorted((CSRC / "native").glob("*.cc")) if p.name != "tsan_stress.cc"]   # that one has a main()
     out = LIB_DIR / "libdtf_native.so"
     LIB_DIR.mkdir(parents=True, exist_ok=True)
     if force and OBJ_DIR.exists():
@@ -107,6 +107,23 @@ def build_native(force: bool = False, jobs: int | None = None) -> Path:
     if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
         _run([cxx, "-shared", "-pthread", "-o", str(out), *map(str, objs)])
     return out
+
+
+def build_tsan_stress(out: Path | None = None) -> Path:
+    """ThreadSanitizer build of the C++ runtime + its stress driver (csrc/native/tsan_stress.cc).
+    Run it with TSAN_OPTIONS=suppressions=csrc/native/tsan.supp; tests/test_tsan_native.py does."""
+    out = out or (OBJ_DIR / "dtf_tsan_stress")
+    out.parent.mkdir(parents=True, exist_ok=True)
+    srcs = sorted((CSRC / "native").glob("*.cc"))
+    last = None
+    for cxx in dict.fromkeys([os.environ.get("CXX", "g++"), "g++", "/usr/bin/g++"]):   # not every g++ ships libtsan
+        try:
+            _run([cxx, "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-pthread", "-msse4.2", "-I", str(REPO / "include"),
+                  *map(str, srcs), "-o", str(out)])
+            return out
+        except Exception as e:
+            last = e
+    raise last
 
 
 def build_all(force: bool = False, verbose: bool = False) -> dict:
