@@ -576,7 +576,10 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
 // Owner of [lo, hi): gradient = sum over `nsrc` ranks' gradient buffers read over NVLink
 // (reduce-scatter), optimizer step on the fp32 master + slots, bf16 (and fp32 tail) written into
 // every peer's working copy (all-gather), all in one pass.  SURVEY.md 2E row K2.
-template <int OPT>
+// WMAX: compile-time bound on the number of gradient replicas held in registers (1 when the sum comes
+// from multimem.ld_reduce); U: independent float4 groups per thread, all of whose loads are issued
+// before anything is consumed (the kernel is a pure stream: ~22 bytes moved per parameter).
+template <int OPT, int WMAX, int U>
 __global__ void __launch_bounds__(256)
 wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, int sum_first,
                       float* __restrict__ master, float* __restrict__ s1, float* __restrict__ s2,
@@ -590,66 +593,77 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
   //   NVLink loads overlap.
   const OptConst oc = stp->oc;
   const long long n4 = (hi - lo) >> 2;
-  for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < n4;
-       q += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long i = lo + q * 4;
-    float4 g[kMaxWorld];
-    float4 gsum = make_float4(0, 0, 0, 0);
-    const bool use_mc_sum = mc != nullptr && sum_first;
-    if (use_mc_sum) {
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                   : "=f"(gsum.x), "=f"(gsum.y), "=f"(gsum.z), "=f"(gsum.w)
-                   : "l"(mc + sl.dense_grad + i * 4)
-                   : "memory");
-    } else {
+  const bool use_mc_sum = mc != nullptr && sum_first;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long q0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q0 < n4; q0 += stride * U) {
+    float4 g[U][WMAX], w[U], a[U], v[U];
 #pragma unroll
-      for (int r = 0; r < kMaxWorld; ++r)
-        if (r < pt.world) g[r] = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
-    }
-    float4 w = *reinterpret_cast<float4*>(master + (i - lo));
-    float4 a = make_float4(0, 0, 0, 0), v = make_float4(0, 0, 0, 0);
-    if (OPT != WD_SGD) a = *reinterpret_cast<float4*>(s1 + (i - lo));
-    if (OPT == WD_ADAM) v = *reinterpret_cast<float4*>(s2 + (i - lo));
-    if (sum_first) {
-      float4 t = gsum;
-      if (!use_mc_sum) {
-#pragma unroll
-        for (int r = 0; r < kMaxWorld; ++r)
-          if (r < pt.world) { t.x += g[r].x; t.y += g[r].y; t.z += g[r].z; t.w += g[r].w; }
-      }
-      opt_update<OPT>(w.x, t.x, a.x, v.x, oc);
-      opt_update<OPT>(w.y, t.y, a.y, v.y, oc);
-      opt_update<OPT>(w.z, t.z, a.z, v.z, oc);
-      opt_update<OPT>(w.w, t.w, a.w, v.w, oc);
-    } else {
-#pragma unroll
-      for (int r = 0; r < kMaxWorld; ++r)
-        if (r < pt.world) {
-          opt_update<OPT>(w.x, g[r].x, a.x, v.x, oc);
-          opt_update<OPT>(w.y, g[r].y, a.y, v.y, oc);
-          opt_update<OPT>(w.z, g[r].z, a.z, v.z, oc);
-          opt_update<OPT>(w.w, g[r].w, a.w, v.w, oc);
-        }
-    }
-    *reinterpret_cast<float4*>(master + (i - lo)) = w;
-    if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + (i - lo)) = a;
-    if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + (i - lo)) = v;
-    uint2 pk;
-    pk.x = pack_bf16x2(w.x, w.y);
-    pk.y = pack_bf16x2(w.z, w.w);
-    if (mc != nullptr) {
-      asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc + sl.wbf16 + i * 2),
-                   "f"(__uint_as_float(pk.x)), "f"(__uint_as_float(pk.y))
-                   : "memory");
-      if (i >= small_begin)
-        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + sl.small_f32 +
-                                                                                            (i - small_begin) * 4),
-                     "f"(w.x), "f"(w.y), "f"(w.z), "f"(w.w)
+    for (int u = 0; u < U; ++u) {
+      const long long q = q0 + u * stride;
+      a[u] = make_float4(0, 0, 0, 0);
+      v[u] = make_float4(0, 0, 0, 0);
+      if (q >= n4) continue;
+      const long long i = lo + q * 4;
+      if (use_mc_sum) {
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(g[u][0].x), "=f"(g[u][0].y), "=f"(g[u][0].z), "=f"(g[u][0].w)
+                     : "l"(mc + sl.dense_grad + i * 4)
                      : "memory");
-    } else {
-      for (int r = 0; r < pt.world; ++r) {
-        *reinterpret_cast<uint2*>(pt.slab[r] + sl.wbf16 + i * 2) = pk;
-        if (i >= small_begin) *reinterpret_cast<float4*>(pt.slab[r] + sl.small_f32 + (i - small_begin) * 4) = w;
+      } else {
+#pragma unroll
+        for (int r = 0; r < WMAX; ++r)
+          if (r < pt.world) g[u][r] = *reinterpret_cast<const float4*>(pt.slab[r] + sl.dense_grad + i * 4);
+      }
+      w[u] = *reinterpret_cast<float4*>(master + (i - lo));
+      if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + (i - lo));
+      if (OPT == WD_ADAM) v[u] = *reinterpret_cast<float4*>(s2 + (i - lo));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long q = q0 + u * stride;
+      if (q >= n4) continue;
+      const long long i = lo + q * 4;
+      if (sum_first) {
+        float4 t = g[u][0];
+        if (!use_mc_sum) {
+#pragma unroll
+          for (int r = 1; r < WMAX; ++r)
+            if (r < pt.world) { t.x += g[u][r].x; t.y += g[u][r].y; t.z += g[u][r].z; t.w += g[u][r].w; }
+        }
+        opt_update<OPT>(w[u].x, t.x, a[u].x, v[u].x, oc);
+        opt_update<OPT>(w[u].y, t.y, a[u].y, v[u].y, oc);
+        opt_update<OPT>(w[u].z, t.z, a[u].z, v[u].z, oc);
+        opt_update<OPT>(w[u].w, t.w, a[u].w, v[u].w, oc);
+      } else {
+#pragma unroll
+        for (int r = 0; r < WMAX; ++r)
+          if (r < pt.world) {
+            opt_update<OPT>(w[u].x, g[u][r].x, a[u].x, v[u].x, oc);
+            opt_update<OPT>(w[u].y, g[u][r].y, a[u].y, v[u].y, oc);
+            opt_update<OPT>(w[u].z, g[u][r].z, a[u].z, v[u].z, oc);
+            opt_update<OPT>(w[u].w, g[u][r].w, a[u].w, v[u].w, oc);
+          }
+      }
+      *reinterpret_cast<float4*>(master + (i - lo)) = w[u];
+      if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + (i - lo)) = a[u];
+      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + (i - lo)) = v[u];
+      uint2 pk;
+      pk.x = pack_bf16x2(w[u].x, w[u].y);
+      pk.y = pack_bf16x2(w[u].z, w[u].w);
+      if (mc != nullptr) {
+        asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc + sl.wbf16 + i * 2),
+                     "f"(__uint_as_float(pk.x)), "f"(__uint_as_float(pk.y))
+                     : "memory");
+        if (i >= small_begin)
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + sl.small_f32 +
+                                                                                              (i - small_begin) * 4),
+                       "f"(w[u].x), "f"(w[u].y), "f"(w[u].z), "f"(w[u].w)
+                       : "memory");
+      } else {
+        for (int r = 0; r < pt.world; ++r) {
+          *reinterpret_cast<uint2*>(pt.slab[r] + sl.wbf16 + i * 2) = pk;
+          if (i >= small_begin) *reinterpret_cast<float4*>(pt.slab[r] + sl.small_f32 + (i - small_begin) * 4) = w[u];
+        }
       }
     }
   }

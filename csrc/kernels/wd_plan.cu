@@ -517,6 +517,8 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.mask_out = train ? p->m1 : nullptr; a.ldmask = p->ldm1;
   a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
   a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
+  // the gather warps also fetch the wide weights of the batch's ids (a separate gather kernel on the side
+  // stream next to layers 2-3 measured the same at 2 GPUs and 6 us slower at 1 GPU: run90)
   a.wide_src = p->wide_src; a.wide_out = p->wide_vals;
   a.bn = 256;
   set_pair(a, 0);
@@ -671,10 +673,22 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st, int which = 3) {
   }
   if (which & 2) {
     const long long dense_n4 = (p->dense_hi - p->dense_lo) / 4;
-    const int dense_grid = p->apply_blocks_per_sm != 8 ? static_cast<int>((dense_n4 + 255) / 256) : num_sms() * 4;
-    wd_dense_apply_kernel<OPT><<<dense_grid, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
-                                                              p->dense_master, p->dense_s1, p->dense_s2, oc,
-                                                              p->dl.small_begin, p->mc);
+    // replicas held in registers: none beyond one when the NVLS sum is used; U float4 groups per thread
+    const bool mc_sum = p->mc != nullptr && p->cfg.sync;
+    const int world = p->cfg.world;
+    auto launch = [&](auto kern, int u) {
+      const long long per_block = 256LL * u;
+      const int dense_grid = p->apply_blocks_per_sm != 8 ? static_cast<int>((dense_n4 + per_block - 1) / per_block)
+                                                         : num_sms() * 4;
+      kern<<<dense_grid > 0 ? dense_grid : 1, 256, 0, st>>>(p->pt, sl, p->dense_lo, p->dense_hi, p->cfg.sync ? 1 : 0,
+                                                             p->dense_master, p->dense_s1, p->dense_s2, oc,
+                                                             p->dl.small_begin, p->mc);
+    };
+    if (mc_sum || world == 1) launch(wd_dense_apply_kernel<OPT, 1, 4>, 4);
+    else if (world == 2) launch(wd_dense_apply_kernel<OPT, 2, 4>, 4);
+    else if (world <= 4) launch(wd_dense_apply_kernel<OPT, 4, 2>, 2);
+    else if (world <= 8) launch(wd_dense_apply_kernel<OPT, 8, 1>, 1);
+    else launch(wd_dense_apply_kernel<OPT, kMaxWorld, 1>, 1);
     count_launch();
     mark(p, st, "dense apply");
   }
