@@ -127,12 +127,24 @@ def main() -> int:
     from distributed_tensorflow_b200.models.wide_deep import WideDeepConfig, WideDeepTrainer
     from distributed_tensorflow_b200.ops import _lib
 
+    verbose = bool(os.environ.get("DTF_BENCH_VERBOSE"))
+
+    def say(msg):
+        if verbose:
+            print("[rank %d] %s" % (rank, msg), file=sys.stderr, flush=True)
+
+    if verbose:
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ.get("DTF_BENCH_WATCHDOG", "45")), exit=True)
     cfg = WideDeepConfig(emb_rows=args.emb_rows, batch=args.batch, optimizer=args.optimizer, sync=(args.mode == "sync"),
                          lr=0.05)
     tr = WideDeepTrainer(cfg, rank=rank, world=world, device=dev)
+    say("trainer created")
     if world > 1:
         tr.attach_peers(dist)
+    say("peers attached")
     tr.init_params()
+    say("params initialised")
     torch.cuda.synchronize()
     host_barrier()
 
@@ -162,6 +174,7 @@ def main() -> int:
             load_static(pool_d[i % args.pool])
             tr.step(s_ids, s_dense, s_labels)
         stream.synchronize()
+        say("eager warm-up done")
         host_barrier()
         graph = None
         G = 1                                         # steps per graph replay
@@ -185,6 +198,7 @@ def main() -> int:
             tr.overlap_reset()
             graph.replay()
             stream.synchronize()
+            say("graph captured and replayed once")
 
         def load_group(pool, base):
             for gi in range(G):
@@ -226,6 +240,8 @@ def main() -> int:
         stream.synchronize()
         host_barrier()
         dev_ms = e0.elapsed_time(e1)
+        if os.environ.get("DTF_BENCH_VERBOSE"):
+            print("[rank %d] device-timed arm done: %.3f ms/step" % (rank, dev_ms / args.steps), file=sys.stderr, flush=True)
         # ---------------- end-to-end region: pinned host -> device every step, loss read back -----
         # Through the public training-loop API (models/wide_deep_loop.py): Ge steps per CUDA-graph
         # replay, the graph holding the pinned-host -> device copies of the Ge input batches (second
@@ -243,6 +259,8 @@ def main() -> int:
         e2.record(stream)
         last_loss = 0.0
         for i in range(0, args.steps, Ge):
+            if os.environ.get("DTF_BENCH_VERBOSE") and i % (100 * Ge) == 0:
+                print("[rank %d] e2e replay %d" % (rank, i // Ge), file=sys.stderr, flush=True)
             loop.run()                             # Ge steps: H2D of their inputs, compute, apply, D2H of the losses
             last_loss = loop.losses()[-1]          # the caller looks at every step's loss (waits for the replay)
         tr.join()

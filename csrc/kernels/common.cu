@@ -94,7 +94,42 @@ bool make_tmap_2d_ex(CUtensorMap* out, const void* base, int elem_bytes, uint64_
 
 }  // namespace dtf
 
+// Copy by kernel.  dst / src may be device memory or pinned host memory (directly addressable under UVA),
+// so this is a host->device or device->host transfer driven by a few SMs instead of a copy-engine
+// operation: inside CUDA graphs that also contain kernels spinning on peer signals, copy-engine memcpy
+// nodes stalled intermittently (bench/stress_overlap.py), kernel nodes do not.
+__global__ void dtf_copy_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, size_t bytes) {
+  const size_t n16 = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0 ? bytes / 16 : 0;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  // four independent 16-byte loads in flight per thread: PCIe round trips are long
+  for (size_t i = t; i < n16; i += 4 * stride) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < n16) v[u] = reinterpret_cast<const uint4*>(src)[i + u * stride];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < n16) reinterpret_cast<uint4*>(dst)[i + u * stride] = v[u];
+  }
+  for (size_t i = n16 * 16 + t; i < bytes; i += stride) dst[i] = src[i];
+}
+
 extern "C" {
+
+int dtf_copy_async(void* dst, const void* src, size_t bytes, int blocks, void* stream) {
+  if (bytes == 0) return 0;
+  if (dst == nullptr || src == nullptr) {
+    dtf::set_error("dtf_copy_async: null pointer");
+    return -2;
+  }
+  if (blocks < 1) blocks = 1;
+  dtf_copy_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(static_cast<uint8_t*>(dst),
+                                                                              static_cast<const uint8_t*>(src), bytes);
+  DTF_CUDA_OK(cudaGetLastError());
+  dtf::count_launch();
+  return 0;
+}
 
 const char* dtf_last_error(void) { return dtf::g_err; }
 

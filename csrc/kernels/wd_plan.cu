@@ -264,6 +264,7 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   p->in_slab<void>("mbx_rows", sl.mbx_rows, static_cast<size_t>(cfg->world) * sh.cap * 4);
   p->in_slab<void>("mbx_dl", sl.mbx_dl, static_cast<size_t>(cfg->world) * sh.cap * 4);
   p->in_slab<void>("mbx_count", sl.mbx_count, kMaxWorld * 4);
+  p->in_slab<void>("signal", sl.signal, kMaxWorld * 64);   // barrier pads (diagnostics: bench/stress_overlap.py)
 
   const size_t ne = static_cast<size_t>(sh.rows_local) * kEmbDim;
   const bool has1 = cfg->optimizer != WD_SGD, has2 = cfg->optimizer == WD_ADAM;

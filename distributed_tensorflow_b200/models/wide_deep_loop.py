@@ -12,16 +12,23 @@ device->host copies of the per-step losses; one ``run()`` then costs one graph l
         loop.run()
         losses = loop.losses()                          # G mean losses, waits for the replay
 
+The transfers inside the graph are small copy *kernels* that read / write the pinned host buffers
+directly (UVA), not copy-engine memcpy nodes: with two or more ranks, graphs that mixed memcpy nodes
+with the kernels that spin on peer signals stalled about once per thousand replays
+(``bench/stress_overlap.py``); all-kernel graphs do not.
+
 In async mode the ps-side applies of step t overlap the compute of step t+1 inside the graph
 (:meth:`WideDeepTrainer.step` with ``overlap=True``); the graph ends with a join, so replays are
 self-contained.
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import List, Optional, Sequence, Tuple
 
 import torch
 
+from ..ops import _lib
 from .wide_deep import WideDeepTrainer
 
 HostBatch = Tuple[torch.Tensor, torch.Tensor, torch.Tensor]
@@ -63,6 +70,14 @@ class GraphedTrainLoop:
             trainer.join()
             self.stream.synchronize()
             trainer.overlap_reset()
+            L = _lib.lib()
+            L.dtf_copy_async.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+
+            def kcopy(dst: torch.Tensor, src: torch.Tensor, blocks: int, stream: torch.cuda.Stream) -> None:
+                _lib.check(L.dtf_copy_async(C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr()),
+                                            dst.numel() * dst.element_size(), blocks, C.c_void_p(stream.cuda_stream)),
+                           "dtf_copy_async")
+
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph, stream=self.stream):
                 self._copy_stream.wait_stream(self.stream)
@@ -70,14 +85,14 @@ class GraphedTrainLoop:
                 with torch.cuda.stream(self._copy_stream):
                     for gi, b in enumerate(self.host_batches):
                         for dst, src in zip(self._dev[gi], b):
-                            dst.copy_(src, non_blocking=True)
+                            kcopy(dst, src, 16, self._copy_stream)          # pinned host -> device over PCIe
                         ev = torch.cuda.Event()
                         ev.record(self._copy_stream)
                         ready.append(ev)
                 for gi in range(self.steps_per_run):
                     self.stream.wait_event(ready[gi])
                     trainer.step(*self._dev[gi])
-                    self._loss_host[gi:gi + 1].copy_(trainer.last_loss_sum(), non_blocking=True)
+                    kcopy(self._loss_host[gi:gi + 1], trainer.last_loss_sum(), 1, self.stream)   # device -> pinned host
                 trainer.join()
                 self.stream.wait_stream(self._copy_stream)
             trainer.overlap_reset()

@@ -121,6 +121,10 @@ int dtf_symm_handle_size(void);
 int dtf_symm_get_handle(void* ptr, void* handle_out);
 int dtf_symm_open_handle(const void* handle, void** out_ptr); /* maps a peer's slab */
 int dtf_symm_close_handle(void* ptr);
+/* Copy by kernel between device memory and / or pinned host memory (UVA pointers): a transfer that is a
+ * kernel node, not a copy-engine node, when captured in a CUDA graph.  blocks x 256 threads. */
+int dtf_copy_async(void* dst, const void* src, size_t bytes, int blocks, void* stream);
+
 int dtf_symm_enable_peer(int peer_device);                    /* same-process peers */
 
 /* Multicast objects (NVLS): one object spans the same leading byte range of every rank's slab; on its
