@@ -9,7 +9,8 @@ N > 1 is launched by ``python -m torch.distributed.run --nproc-per-node N ... be
 (one rank per GPU).  Rank 0 prints ONE JSON line.  `value` is device-timed (CUDA events around the
 K steps, max over ranks) with inputs resident on the device; `e2e` repeats the measurement through
 the public API with a pinned-host -> device copy of every step's inputs and a device -> host read of
-the step's loss inside the timed region (GraphedTrainLoop: the copies are nodes of the replayed graph).  Synthetic data, random-init weights (no network).
+the step's loss inside the timed region (GraphedTrainLoop: the copies are kernels of the replayed graph
+that read / write the pinned host buffers over PCIe).  Synthetic data, random-init weights (no network).
 """
 from __future__ import annotations
 
@@ -244,8 +245,8 @@ def main() -> int:
             print("[rank %d] device-timed arm done: %.3f ms/step" % (rank, dev_ms / args.steps), file=sys.stderr, flush=True)
         # ---------------- end-to-end region: pinned host -> device every step, loss read back -----
         # Through the public training-loop API (models/wide_deep_loop.py): Ge steps per CUDA-graph
-        # replay, the graph holding the pinned-host -> device copies of the Ge input batches (second
-        # stream, running ahead of the compute) and the device -> host copies of the Ge losses.
+        # replay, the graph holding the pinned-host -> device copies of the Ge input batches (copy kernels
+        # on a second stream, running ahead of the compute) and the device -> host copies of the Ge losses.
         from distributed_tensorflow_b200.models.wide_deep_loop import GraphedTrainLoop
         Ge = next(g for g in (10, 8, 5, 4, 2, 1) if args.steps % g == 0)
         tr.join()
