@@ -95,7 +95,7 @@ int dtf_push_gemm_bf16(const void* dY, long long lddy, const void* W, long long 
 /* Same computation as dtf_pull_gemm_bf16 for callers that cannot allocate device memory (a process
  * whose device memory was all handed to its own pool at start-up, a plug-in inside one, or a
  * request path that cannot tolerate cudaMalloc's device-wide synchronisation): the scratch is a
- * static device array inside the library (about 32 KiB per GPU that loads the library, held until
+ * static device array inside the library (about 256 KiB per GPU that loads the library, held until
  * exit), so there is no scratch argument and M is limited to dtf_pull_gemm_noalloc_max_rows()
  * (1,048,576); larger M is rejected with an error.  The call allocates nothing.  All calls on a
  * device share that array, which keeps the previous call's contents (the used part is cleared at the
