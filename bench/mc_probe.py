@@ -33,9 +33,7 @@ tr.join()
 torch.cuda.synchronize()
 dist.barrier()
 shard = tr.named_shards()
-key = [k for k in shard if "dense" in k and "master" in k or k.endswith("dense")]
 chk = {k: float(v.double().abs().sum()) for k, v in shard.items() if v.dtype == torch.float32 and v.numel() < 10_000_000}
-w = tr.buffer("wbf16", torch.bfloat16) if False else None
 print("rank %d multicast=%s mode=%s losses=%s" % (rank, tr.multicast, mode, ["%.6f" % l for l in losses]), flush=True)
 print("rank %d checksums %s" % (rank, {k: "%.6f" % v for k, v in sorted(chk.items())[:6]}), flush=True)
 dist.barrier()

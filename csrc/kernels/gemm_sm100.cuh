@@ -12,9 +12,11 @@
 //   warp 0      : TMA producer (one elected lane)
 //   warp 1      : TMEM allocator + tcgen05.mma issuer (one lane)
 //   warps 2..5  : epilogue; warp w owns TMEM lanes [32*(w%4), 32*(w%4)+32)
-// Fused variants add gather warps (6..9) that pull embedding rows from peer HBM into the A
-// buffer while the MMA warps work on earlier tiles, and an epilogue that scatters output rows to
-// peer mailboxes (see fused_pull_gemm / fused_push_gemm instantiations).
+// The fused pull (GATHER) adds warps 6..17 = gather warps that fetch embedding rows from the owning
+// ranks' HBM (local or peer over NVLink) into the A operand buffer, and warp 18 = watcher that turns
+// their arrival counters into "k-blocks ready" for the TMA producer, so that the MMAs trail the gather
+// k-block by k-block (608 threads).  The fused push is an epilogue that scatters output rows to peer
+// mailboxes.  CTAS = 2 runs every variant on CTA pairs (clusters of two, tcgen05.mma.cta_group::2).
 #pragma once
 
 #include "sm100_ptx.cuh"
