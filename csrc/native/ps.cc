@@ -16,6 +16,7 @@
 #include <netinet/tcp.h>
 #include <poll.h>
 #include <sys/socket.h>
+#include <sys/uio.h>
 #include <sys/time.h>
 #include <unistd.h>
 
@@ -52,8 +53,14 @@ struct Writer {
     i32(static_cast<int32_t>(v.size()));
     s.append(v);
   }
+  // length, pad count, pad, payload: the payload starts at a multiple of 4 bytes from the start of the
+  // message body, and both ends keep the body 4-byte aligned in memory, so float payloads can be
+  // consumed in place
   void bytes(const void* p, size_t n) {
     i64(static_cast<int64_t>(n));
+    const size_t pad = (4 - ((s.size() + 1) & 3)) & 3;
+    u8(static_cast<uint8_t>(pad));
+    s.append(pad, '\0');
     s.append(static_cast<const char*>(p), n);
   }
 };
@@ -91,6 +98,9 @@ struct Reader {
   }
   const char* bytes(size_t* n) {
     const int64_t len = i64();
+    const size_t pad = u8();
+    if (pad > 3 || !need(pad)) { ok = false; *n = 0; return nullptr; }
+    p += pad;
     if (len < 0 || !need(static_cast<size_t>(len))) { ok = false; *n = 0; return nullptr; }
     const char* q = p;
     p += len;
@@ -124,6 +134,47 @@ static bool recv_all(int fd, void* buf, size_t n) {
     n -= static_cast<size_t>(r);
   }
   return true;
+}
+
+// header + body with one gather write: the body (up to hundreds of MB of gradients or values) is never
+// copied into a contiguous frame
+static bool send_frame(int fd, const void* hdr, size_t hn, const std::string& body) {
+  struct iovec iov[2];
+  iov[0].iov_base = const_cast<void*>(hdr);
+  iov[0].iov_len = hn;
+  iov[1].iov_base = const_cast<char*>(body.data());
+  iov[1].iov_len = body.size();
+  int first = 0;
+  while (first < 2) {
+    if (iov[first].iov_len == 0) {
+      ++first;
+      continue;
+    }
+    struct msghdr m{};
+    m.msg_iov = iov + first;
+    m.msg_iovlen = static_cast<size_t>(2 - first);
+    const ssize_t w = ::sendmsg(fd, &m, MSG_NOSIGNAL);
+    if (w <= 0) {
+      if (w < 0 && errno == EINTR) continue;
+      return false;
+    }
+    size_t left = static_cast<size_t>(w);
+    while (left > 0 && first < 2) {
+      const size_t take = left < iov[first].iov_len ? left : iov[first].iov_len;
+      iov[first].iov_base = static_cast<char*>(iov[first].iov_base) + take;
+      iov[first].iov_len -= take;
+      left -= take;
+      if (iov[first].iov_len == 0) ++first;
+    }
+  }
+  return true;
+}
+static void tune_socket(int fd) {
+  int one = 1;
+  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+  int sz = 4 << 20;   // dense gradient pushes are megabytes: let a whole message sit in the socket buffers
+  setsockopt(fd, SOL_SOCKET, SO_SNDBUF, &sz, sizeof(sz));
+  setsockopt(fd, SOL_SOCKET, SO_RCVBUF, &sz, sizeof(sz));
 }
 
 // ---------------------------------------------------------------- store
@@ -203,6 +254,15 @@ __attribute__((noinline)) static void hogwild_read_beta_powers(Store* st, float*
 __attribute__((noinline)) static void hogwild_advance_beta_powers(Store* st) {
   st->find("beta1_power")->f()[0] *= kAdamB1;
   st->find("beta2_power")->f()[0] *= kAdamB2;
+}
+
+// float view of a gradient inside the receive buffer: used in place when it happens to be 4-byte
+// aligned, copied into `tmp` otherwise
+static const float* grad_view(const char* g, size_t nbytes, std::vector<float>& tmp) {
+  if ((reinterpret_cast<uintptr_t>(g) & 3u) == 0) return reinterpret_cast<const float*>(g);
+  tmp.resize(nbytes / 4);
+  memcpy(tmp.data(), g, tmp.size() * 4);
+  return tmp.data();
 }
 
 static int apply_one(Store* st, const std::string& name, int opt, float lr, const float* g, size_t n,
@@ -334,9 +394,8 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       if (opt == DTFN_OPT_ADAM) {
         hogwild_read_beta_powers(&store, &b1p, &b2p);
       }
-      std::vector<float> grad(n / 4);
-      memcpy(grad.data(), g, grad.size() * 4);
-      const int rc = apply_one(&store, name, opt, lr, grad.data(), grad.size(), b1p, b2p);
+      std::vector<float> tmp;
+      const int rc = apply_one(&store, name, opt, lr, grad_view(g, n, tmp), n / 4, b1p, b2p);
       if (rc == 0 && opt == DTFN_OPT_ADAM) {
         hogwild_advance_beta_powers(&store);
       }
@@ -356,9 +415,8 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
         size_t n;
         const char* g = r.bytes(&n);
         if (!r.ok) return -1;
-        std::vector<float> grad(n / 4);
-        memcpy(grad.data(), g, grad.size() * 4);
-        const int rc = apply_one(&store, names.back(), opt, lr, grad.data(), grad.size(), b1p, b2p);
+        std::vector<float> tmp;
+        const int rc = apply_one(&store, names.back(), opt, lr, grad_view(g, n, tmp), n / 4, b1p, b2p);
         if (rc != 0) return rc;
       }
       if (opt == DTFN_OPT_ADAM && k > 0) {
@@ -484,28 +542,27 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
 }
 
 void dtfn_server::handle(int fd) {
-  int one = 1;
-  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
-  std::string buf;
+  tune_socket(fd);
+  std::string buf;   // only ever grows: resize() would zero-fill megabytes per request otherwise
   for (;;) {
     uint32_t len;
     if (!recv_all(fd, &len, 4)) break;
     if (len < 1 || len > (1u << 30)) break;
-    buf.resize(len);
-    if (!recv_all(fd, &buf[0], len)) break;
+    // the op byte lands at offset 3 so that the body behind it starts 4-byte aligned
+    if (buf.size() < static_cast<size_t>(len) + 3) buf.resize(static_cast<size_t>(len) + 3);
+    if (!recv_all(fd, &buf[3], len)) break;
     if (drop.load() > 0 && drop.fetch_sub(1) > 0) break;  // fault injection: vanish mid-request
-    Reader r(buf.data() + 1, len - 1);
+    Reader r(buf.data() + 4, len - 1);
     Writer w;
-    const uint8_t op = static_cast<uint8_t>(buf[0]);
+    const uint8_t op = static_cast<uint8_t>(buf[3]);
     int status = dispatch(op, r, w);
     if (!r.ok) status = -1;
-    std::string out;
+    char hdr[8];
     const uint32_t olen = static_cast<uint32_t>(4 + w.s.size());
-    out.append(reinterpret_cast<const char*>(&olen), 4);
     const int32_t st = status;
-    out.append(reinterpret_cast<const char*>(&st), 4);
-    out.append(w.s);
-    if (!send_all(fd, out.data(), out.size())) break;
+    memcpy(hdr, &olen, 4);
+    memcpy(hdr + 4, &st, 4);
+    if (!send_frame(fd, hdr, 8, w.s)) break;
     if (op == OP_SHUTDOWN) break;
   }
   ::shutdown(fd, SHUT_RDWR);
@@ -607,12 +664,11 @@ struct dtfn_client {
   // sends one request and receives the response payload into `resp`; returns status or <= -100 on
   // transport failure
   int call(uint8_t op, const Writer& w) {
-    std::string out;
+    char hdr[5];
     const uint32_t len = static_cast<uint32_t>(1 + w.s.size());
-    out.append(reinterpret_cast<const char*>(&len), 4);
-    out.push_back(static_cast<char>(op));
-    out.append(w.s);
-    if (!send_all(fd, out.data(), out.size())) {
+    memcpy(hdr, &len, 4);
+    hdr[4] = static_cast<char>(op);
+    if (!send_frame(fd, hdr, 5, w.s)) {
       set_error("client: send to %s:%d failed: %s", host.c_str(), port, strerror(errno));
       return -100;
     }
@@ -671,8 +727,7 @@ dtfn_client* dtfn_client_connect(const char* host, int port, int timeout_ms) {
     ::close(fd);
     return nullptr;
   }
-  int one = 1;
-  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+  tune_socket(fd);
   auto* c = new dtfn_client();
   c->fd = fd;
   c->host = host;
@@ -771,6 +826,9 @@ int dtfn_client_push_pull(dtfn_client* c, int k, const char* const* names, int o
                           long long step_inc, float* const* dst, long long* step_out) {
   std::lock_guard<std::mutex> l(c->mu);
   Writer w;
+  size_t total = 64;
+  for (int i = 0; i < k; ++i) total += lens[i] * 4 + strlen(names[i]) + 16;
+  w.s.reserve(total);
   w.i32(k);
   w.i32(optimizer);
   w.f32(lr);
