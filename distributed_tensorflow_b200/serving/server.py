@@ -78,12 +78,102 @@ class ModelServer:
             if alias not in data:
                 raise ValueError("missing input %r (signature inputs: %s)" % (alias, sorted(self.input_dtypes)))
             inputs[alias] = np.asarray(data[alias]).astype(dt)
+        out = self._run(inputs)
+        return {k: np.asarray(out[k]).tolist() for k in self.output_names}
+
+    def _run(self, inputs: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
         n = {v.shape[0] for v in inputs.values() if v.ndim > 0}
         if len(n) > 1:
             raise ValueError("inputs disagree on batch size: %s" % sorted(n))
         out = self._impl(inputs)
         self.requests += 1
-        return {k: np.asarray(out[k]).tolist() for k in self.output_names}
+        return out
+
+    def predict_json(self, body: bytes) -> bytes:
+        """Request body -> response body.  Bodies made of rectangular numeric arrays (the normal case) are
+        parsed and formatted by the C++ fast path (``csrc/native/json_fast.cc``); anything else goes through
+        the generic ``json`` module with identical results."""
+        fast = _FastJson.get()
+        if fast is not None and body and b'"data"' not in body:
+            inputs = {}
+            for alias, dt in self.input_dtypes.items():
+                arr = fast.parse(body, alias)
+                if arr is None:
+                    inputs = None
+                    break
+                inputs[alias] = arr.astype(dt)
+            if inputs is not None:
+                out = self._run(inputs)
+                parts = []
+                for k in self.output_names:
+                    txt = fast.format(np.asarray(out[k]))
+                    if txt is None:
+                        parts = None
+                        break
+                    parts.append(json.dumps(k).encode() + b": " + txt)
+                if parts is not None:
+                    return b"{" + b", ".join(parts) + b"}"
+                return json.dumps({k: np.asarray(out[k]).tolist() for k in self.output_names}).encode()
+        return json.dumps(self.predict(json.loads(body or b"{}"))).encode()
+
+
+class _FastJson:
+    """ctypes binding of the native JSON fast path; ``get()`` returns None when the library is missing."""
+
+    _inst = None
+    _tried = False
+
+    @classmethod
+    def get(cls):
+        if not cls._tried:
+            cls._tried = True
+            try:
+                from .. import _native
+                cls._inst = cls(_native.lib())
+            except Exception:       # noqa: BLE001  (no native library: generic path only)
+                cls._inst = None
+        return cls._inst
+
+    def __init__(self, L):
+        import ctypes as C
+        self.C, self.L = C, L
+        L.dtfn_json_numeric_array.restype = C.c_longlong
+        L.dtfn_json_numeric_array.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_void_p, C.c_size_t,
+                                              C.POINTER(C.c_longlong), C.POINTER(C.c_int)]
+        L.dtfn_json_format_array.restype = C.c_longlong
+        L.dtfn_json_format_array.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_longlong), C.c_int, C.c_void_p, C.c_size_t]
+
+    def parse(self, body: bytes, key: str):
+        C = self.C
+        cap = len(body) // 2 + 1                     # every number takes at least two bytes ("1,")
+        buf = np.empty(cap, np.float64)
+        dims = (C.c_longlong * 4)()
+        nd = C.c_int(0)
+        n = self.L.dtfn_json_numeric_array(body, len(body), key.encode(), buf.ctypes.data, cap, dims, C.byref(nd))
+        if n < 0:
+            return None
+        shape = tuple(int(dims[i]) for i in range(nd.value))
+        if int(np.prod(shape)) != n:
+            return None
+        return buf[:n].reshape(shape)
+
+    def format(self, arr: np.ndarray):
+        C = self.C
+        if arr.ndim < 1 or arr.ndim > 4:
+            return None
+        if np.issubdtype(arr.dtype, np.integer):
+            data, kind = np.ascontiguousarray(arr, np.int64), 1
+        elif np.issubdtype(arr.dtype, np.floating):
+            data, kind = np.ascontiguousarray(arr, np.float32), 0
+        else:
+            return None
+        dims = (C.c_longlong * 4)(*arr.shape)
+        cap = data.size * (26 + 2 * arr.ndim) + 16
+        out = C.create_string_buffer(cap)
+        n = self.L.dtfn_json_format_array(data.ctypes.data, kind, dims, arr.ndim, out, cap)
+        if n <= 0:
+            return None
+        return out.raw[:n]
 
 
 def make_http_server(model: ModelServer, host: str = "0.0.0.0", port: int = 8500) -> ThreadingHTTPServer:
@@ -91,7 +181,9 @@ def make_http_server(model: ModelServer, host: str = "0.0.0.0", port: int = 8500
         protocol_version = "HTTP/1.1"
 
         def _send(self, code: int, payload: dict) -> None:
-            body = json.dumps(payload).encode()
+            self._send_raw(code, json.dumps(payload).encode())
+
+        def _send_raw(self, code: int, body: bytes) -> None:
             self.send_response(code)
             self.send_header("Content-Type", "application/json")
             self.send_header("Content-Length", str(len(body)))
@@ -106,8 +198,7 @@ def make_http_server(model: ModelServer, host: str = "0.0.0.0", port: int = 8500
         def do_POST(self):  # noqa: N802
             try:
                 n = int(self.headers.get("Content-Length", "0"))
-                req = json.loads(self.rfile.read(n) or b"{}")
-                self._send(200, model.predict(req))
+                self._send_raw(200, model.predict_json(self.rfile.read(n)))
             except (ValueError, KeyError, TypeError) as e:
                 self._send(400, {"error": str(e)})
             except Exception as e:  # pragma: no cover

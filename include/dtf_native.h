@@ -93,6 +93,18 @@ void dtfn_apply_ftrl(float* var, float* accum, float* linear, const float* g, si
 void dtfn_apply_rmsprop(float* var, float* ms, float* mom, const float* g, size_t n, float lr, float decay,
                         float momentum, float eps);
 
+/* ---- serving JSON fast path --------------------------------------------------------------- *
+ * The predict endpoint's bodies are objects of rectangular nested numeric arrays (reference
+ * README.md:40).  dtfn_json_numeric_array finds `key` at the top level (or inside a top-level "data"
+ * envelope) and parses its value into out (row-major doubles): returns the number of values and fills
+ * dims[0..*ndims) (ndims <= 4); -1 key absent, -2 not a plain rectangular numeric array (use a generic
+ * JSON parser), -3 out too small.  dtfn_json_format_array writes a row-major array as nested JSON
+ * arrays (kind 0: float32 in the shortest form that round-trips, 1: int64); returns bytes written or
+ * minus the capacity it needs. */
+long long dtfn_json_numeric_array(const char* body, size_t n, const char* key, double* out, size_t cap,
+                                  long long* dims, int* ndims);
+long long dtfn_json_format_array(const void* data, int kind, const long long* dims, int ndims, char* out, size_t cap);
+
 /* ---- parameter-server transport ------------------------------------------------------------ *
  * Replaces the in-process gRPC tf.train.Server (MasterService + WorkerService), the Send/Recv
  * rendezvous and the shared-name FIFOQueue resource (reference trainer/task.py:118-122,
