@@ -230,7 +230,13 @@ def run_wide_deep(flags) -> None:
     torch.cuda.set_stream(torch.cuda.Stream(device=tr.device, priority=-1))   # compute outranks the ps-side apply
     for epoch in range(flags.max_epochs):
         for _ in range(steps_per_epoch):
-            tr.step(*synthetic_batch(cfg, gen, tr.device))
+            batch = synthetic_batch(cfg, gen, torch.device("cpu"))
+            if d.world > 1:
+                # copy-engine transfers are kept away from the device-barrier kernels of the overlapped apply
+                # (they stalled intermittently when mixed inside CUDA graphs); the host-side
+                # batch generation above is far longer than the apply, so this wait is normally already over
+                tr.join()
+            tr.step(*(t.to(tr.device) for t in batch))
             step += 1
         if epoch % flags.checkpoint_period == 0:
             loss = float(tr.last_loss_sum()) / cfg.batch
