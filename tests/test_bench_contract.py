@@ -27,3 +27,11 @@ def test_graft_entry_build_produces_in_tree_libraries():
     for name in ("libdtf_kernels.so", "libdtf_native.so"):
         assert os.path.getsize(os.path.join(lib, name)) > 100_000
     assert callable(g.smoke)
+
+
+def test_packaging_stub_lists_the_three_packages():
+    p = subprocess.run([sys.executable, "setup.py", "--name", "--version"], capture_output=True, text=True, timeout=120, cwd=REPO)
+    assert p.returncode == 0, p.stderr[-1000:]
+    assert p.stdout.split()[-2:] == ["distributed_tensorflow_b200", "1.0"]
+    for pkg in ("trainer", "auto_stop_ps", "distributed_tensorflow_b200"):
+        assert os.path.isfile(os.path.join(REPO, pkg, "__init__.py"))
