@@ -1,5 +1,6 @@
 """Flags, TF_CONFIG parsing, ClusterSpec and placement (reference trainer/task.py:17-31,110-127)."""
 import json
+import os
 
 import pytest
 
@@ -99,3 +100,28 @@ def test_row_and_range_shards():
     assert b[0][0] == 0 and b[-1][1] == 1000 and all(b[i][1] == b[i + 1][0] for i in range(2))
     assert all(lo % 256 == 0 or lo == 1000 for lo, _ in b)
     assert [g.owner(i) for i in (0, 511, 512, 999)] == [0, 0, 1, 1]
+
+
+def test_entry_points_keep_the_reference_flag_names_and_defaults():
+    """SURVEY.md A2 / A2' / A2'': same nine (eight) flags, same defaults, max_epochs 10 / 20 / 100."""
+    import json
+    import subprocess
+    import sys
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    common = {"checkpoint_period": 1, "learning_rate": 0.01, "optimizer": "sgd"}
+    expect = {
+        "trainer.task": dict(common, max_epochs=10, checkpoint_path="./checkpoint/", output_path="./tensorboard/",
+                             model_path="./model/", saved_model_path="./saved_model/", model_version=1),
+        "auto_stop_ps.task": dict(common, max_epochs=20, checkpoint_path="./checkpoint/", output_path="./tensorboard/",
+                                  model_path="./model/", saved_model_path="./saved_model/", model_version=1),
+        "trainer.task_supervisor": dict(common, max_epochs=100, checkpoint_dir="./checkpoint/", tensorboard_dir="./tensorboard/",
+                                        export_version=1, export_dir="/tmp/linear_model/"),
+    }
+    for mod, want in expect.items():
+        code = "import json, sys; sys.argv=['x']; import %s as m; print(json.dumps(m.FLAGS.flag_values_dict()))" % mod
+        p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120, cwd=repo,
+                           env=dict(os.environ, PYTHONPATH=repo))
+        assert p.returncode == 0, p.stderr[-1500:]
+        got = json.loads(p.stdout.strip().splitlines()[-1])
+        for k, v in want.items():
+            assert got[k] == v, (mod, k, got.get(k), v)
