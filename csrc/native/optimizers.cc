@@ -5,13 +5,22 @@
 
 #include "../../include/dtf_native.h"
 
-extern "C" {
+// The three optimizers that see large tensors get an AVX2 clone next to the baseline (SSE) build; glibc's
+// ifunc resolver picks one at load time, so the same .so runs on any x86-64.  sqrt and divide stay the
+// IEEE instructions (no rsqrt approximations, no FMA contraction), i.e. results are bit-identical to the
+// scalar loops.  The names start with hogwild_apply_ so that csrc/native/tsan.supp can name them.
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(__SANITIZE_THREAD__)
+#define DTFN_CLONES __attribute__((target_clones("avx2", "default"), optimize("O3", "no-math-errno", "no-trapping-math")))
+#else
+#define DTFN_CLONES
+#endif
 
-void dtfn_apply_sgd(float* var, const float* g, size_t n, float lr) {
+DTFN_CLONES static void hogwild_apply_sgd(float* __restrict__ var, const float* __restrict__ g, size_t n, float lr) {
   for (size_t i = 0; i < n; ++i) var[i] -= lr * g[i];
 }
 
-void dtfn_apply_adagrad(float* var, float* accum, const float* g, size_t n, float lr) {
+DTFN_CLONES static void hogwild_apply_adagrad(float* __restrict__ var, float* __restrict__ accum,
+                                              const float* __restrict__ g, size_t n, float lr) {
   for (size_t i = 0; i < n; ++i) {
     const float a = accum[i] + g[i] * g[i];
     accum[i] = a;
@@ -19,9 +28,9 @@ void dtfn_apply_adagrad(float* var, float* accum, const float* g, size_t n, floa
   }
 }
 
-void dtfn_apply_adam(float* var, float* m, float* v, const float* g, size_t n, float lr, float beta1, float beta2,
-                     float eps, float beta1_power, float beta2_power) {
-  const float lr_t = lr * sqrtf(1.f - beta2_power) / (1.f - beta1_power);
+DTFN_CLONES static void hogwild_apply_adam(float* __restrict__ var, float* __restrict__ m, float* __restrict__ v,
+                                           const float* __restrict__ g, size_t n, float lr_t, float beta1, float beta2,
+                                           float eps) {
   for (size_t i = 0; i < n; ++i) {
     const float mi = beta1 * m[i] + (1.f - beta1) * g[i];
     const float vi = beta2 * v[i] + (1.f - beta2) * g[i] * g[i];
@@ -29,6 +38,20 @@ void dtfn_apply_adam(float* var, float* m, float* v, const float* g, size_t n, f
     v[i] = vi;
     var[i] -= lr_t * mi / (sqrtf(vi) + eps);
   }
+}
+
+extern "C" {
+
+void dtfn_apply_sgd(float* var, const float* g, size_t n, float lr) { hogwild_apply_sgd(var, g, n, lr); }
+
+void dtfn_apply_adagrad(float* var, float* accum, const float* g, size_t n, float lr) {
+  hogwild_apply_adagrad(var, accum, g, n, lr);
+}
+
+void dtfn_apply_adam(float* var, float* m, float* v, const float* g, size_t n, float lr, float beta1, float beta2,
+                     float eps, float beta1_power, float beta2_power) {
+  const float lr_t = lr * sqrtf(1.f - beta2_power) / (1.f - beta1_power);
+  hogwild_apply_adam(var, m, v, g, n, lr_t, beta1, beta2, eps);
 }
 
 void dtfn_apply_adadelta(float* var, float* accum, float* accum_update, const float* g, size_t n, float lr,
