@@ -65,40 +65,10 @@ def build_signature_def(model):
     return sig
 
 
-def _toy_graph_def(graph_def, model) -> None:
-    """Device-free GraphDef naming the tensors the signature refers to."""
-    def node(name, op, inputs=(), dtype=None, shape=None, attr_T=None):
-        n = graph_def.node.add()
-        n.name, n.op = name, op
-        n.input.extend(inputs)
-        if dtype is not None:
-            n.attr["dtype"].type = _NP_TO_DT[np.dtype(dtype)]
-        if attr_T is not None:
-            n.attr["T"].type = _NP_TO_DT[np.dtype(attr_T)]
-        if shape is not None:
-            sh = n.attr["shape"].shape
-            for d in shape:
-                sh.dim.add().size = d
-        return n
-
-    if getattr(model, "name", "") == "linear":
-        node("Placeholder", "Placeholder", dtype=np.int32, shape=(-1, 1))
-        node("Identity", "Identity", ["Placeholder"], attr_T=np.int32)
-        node("Placeholder_1", "Placeholder", dtype=np.float32, shape=(-1, 1))
-        node("Placeholder_2", "Placeholder", dtype=np.float32, shape=(-1, 1))
-        for v in model.variables:
-            node(v.name, "VariableV2", dtype=v.dtype, shape=v.initial.shape)
-            node(v.name + "/read", "Identity", [v.name], attr_T=v.dtype)
-        node("Mul_1", "Mul", ["Placeholder_1", "weight/read"], attr_T=np.float32)
-        node("add", "Add", ["Mul_1", "bias/read"], attr_T=np.float32)
-    else:
-        for alias, (tname, dt, shape) in model.signature_inputs.items():
-            node(tname.split(":")[0], "Placeholder", dtype=dt, shape=shape)
-        for alias, (tname, dt, shape) in model.signature_outputs.items():
-            node(tname.split(":")[0], "DtfModelOutput", attr_T=dt)
-    node("legacy_init_op", "NoOp")
-    node("save/Const", "Const", dtype=None)
-    node("save/restore_all", "NoOp")
+def _toy_graph_def(graph_def, model, tensors=None) -> dict:
+    """Device-free GraphDef of the model in TF-1 layout (export/graph_def.py); returns the SaverDef names."""
+    from .graph_def import build_graph_def
+    return build_graph_def(graph_def, model, tensors)
 
 
 class SavedModelBuilder:
@@ -128,12 +98,12 @@ class SavedModelBuilder:
         mg.meta_info_def.tags.extend(tags)
         mg.meta_info_def.tensorflow_version = "1.15.0"
         mg.meta_info_def.tensorflow_git_version = "distributed_tensorflow_b200"
-        _toy_graph_def(mg.graph_def, model)
+        saver_names = _toy_graph_def(mg.graph_def, model, tensors)
         mg.graph_def.versions.producer = 134
         sd = mg.saver_def
-        sd.filename_tensor_name = "save/Const:0"
-        sd.save_tensor_name = "save/control_dependency:0"
-        sd.restore_op_name = "save/restore_all"
+        sd.filename_tensor_name = saver_names["filename_tensor_name"]
+        sd.save_tensor_name = saver_names["save_tensor_name"]
+        sd.restore_op_name = saver_names["restore_op_name"]
         sd.max_to_keep = 5
         sd.sharded = True
         sd.keep_checkpoint_every_n_hours = 10000.0

@@ -8,9 +8,13 @@ example, the F sparse ids followed by the dense features.
 """
 from __future__ import annotations
 
+import threading
 from typing import Dict
 
 import numpy as np
+
+# float32 represents every integer only below 2**24; ids at or above that must arrive as integers / float64
+_F32_EXACT = 1 << 24
 
 
 def assemble(variables: Dict[str, np.ndarray], name: str, world: int) -> np.ndarray:
@@ -43,6 +47,10 @@ class WideDeepPredictor:
         if device == "cuda" and not use_gpu:
             raise RuntimeError("device=cuda requested but no GPU is visible")
         self.max_batch = max_batch
+        self.emb_rows = int(config.get("emb_rows", emb.shape[0]))
+        # One set of staging buffers and one plan serve every request: the HTTP layer is threaded
+        # (serving/server.py), so the GPU path is serialised here.  Requests queue for ~0.1 ms each.
+        self._gpu_lock = threading.Lock()
         if use_gpu:
             self._init_gpu(emb, wide, flat)
         else:
@@ -73,6 +81,11 @@ class WideDeepPredictor:
     def _predict_gpu(self, ids: np.ndarray, dense: np.ndarray) -> np.ndarray:
         torch = self._torch
         out = np.empty(ids.shape[0], np.float32)
+        with self._gpu_lock:
+            self._predict_gpu_locked(torch, ids, dense, out)
+        return out
+
+    def _predict_gpu_locked(self, torch, ids, dense, out) -> None:
         for lo in range(0, ids.shape[0], self.max_batch):
             n = min(self.max_batch, ids.shape[0] - lo)
             self._h_ids[:n].copy_(torch.from_numpy(ids[lo:lo + n]))
@@ -83,7 +96,6 @@ class WideDeepPredictor:
             self._h_out[:n].copy_(p, non_blocking=True)
             torch.cuda.current_stream().synchronize()
             out[lo:lo + n] = self._h_out[:n].numpy()
-        return out
 
     # ------------------------------------------------------------------ CPU
     def _init_cpu(self, emb, wide, flat):
@@ -118,10 +130,27 @@ class WideDeepPredictor:
     # ------------------------------------------------------------------ endpoint
     def predict(self, inputs: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
         keys = np.asarray(inputs["keys"]).astype(np.int32)
-        feats = np.asarray(inputs["features"], np.float32)
-        if feats.ndim != 2 or feats.shape[1] != self.slots + self.dense_in:
-            raise ValueError("features must be [batch, %d] (ids then dense values)" % (self.slots + self.dense_in))
-        ids = np.ascontiguousarray(feats[:, : self.slots].astype(np.int32))
-        dense = np.ascontiguousarray(feats[:, self.slots:])
+        feats = np.asarray(inputs["features"])
+        if feats.ndim != 2:
+            raise ValueError("features must be a [batch, n] array")
+        if "ids" in inputs:
+            # integer ids travel on their own (exact for any table size); features then holds only the dense part
+            ids = np.asarray(inputs["ids"])
+            if ids.ndim != 2 or ids.shape[1] != self.slots or ids.shape[0] != feats.shape[0]:
+                raise ValueError("ids must be [batch, %d]" % self.slots)
+            if feats.shape[1] != self.dense_in:
+                raise ValueError("with ids given, features must be [batch, %d] (dense values only)" % self.dense_in)
+            dense = feats
+        else:
+            if feats.shape[1] != self.slots + self.dense_in:
+                raise ValueError("features must be [batch, %d] (ids then dense values)" % (self.slots + self.dense_in))
+            ids = feats[:, : self.slots]
+            dense = feats[:, self.slots:]
+        if ids.dtype == np.float32 and ids.size and float(np.abs(ids).max()) >= _F32_EXACT:
+            raise ValueError("sparse ids >= 2**24 are not exact in float32; send them as integers (input 'ids') or float64")
+        if ids.dtype.kind == "f" and ids.size and not np.array_equal(ids, np.rint(ids)):
+            raise ValueError("sparse ids must be integers")
+        ids = np.ascontiguousarray(np.mod(ids.astype(np.int64), self.emb_rows).astype(np.int32))
+        dense = np.ascontiguousarray(dense, np.float32)
         p = self._predict_gpu(ids, dense) if self.backend == "cuda" else self._predict_cpu(ids, dense)
         return {"keys": keys, "prediction": p.reshape(-1, 1)}

@@ -55,6 +55,12 @@ class ModelServer:
         self.input_dtypes = {k: _DT_TO_NP[v.dtype] for k, v in self.signature.inputs.items()}
         self.output_names = sorted(self.signature.outputs)
         self.model_name = self.description.get("model", "linear")
+        # wide-and-deep: the sparse ids ride in `features` (or in an extra integer input `ids`); keep
+        # float64 up to the predictor so that ids >= 2**24 are not rounded by a float32 cast
+        self.optional_inputs: Dict[str, type] = {}
+        if self.model_name == "wide_deep":
+            self.input_dtypes["features"] = np.float64
+            self.optional_inputs["ids"] = np.int64
         self._impl = self._build(device)
         self.requests = 0
 
@@ -78,6 +84,9 @@ class ModelServer:
             if alias not in data:
                 raise ValueError("missing input %r (signature inputs: %s)" % (alias, sorted(self.input_dtypes)))
             inputs[alias] = np.asarray(data[alias]).astype(dt)
+        for alias, dt in self.optional_inputs.items():
+            if alias in data:
+                inputs[alias] = np.asarray(data[alias]).astype(dt)
         out = self._run(inputs)
         return {k: np.asarray(out[k]).tolist() for k in self.output_names}
 
@@ -102,6 +111,14 @@ class ModelServer:
                     inputs = None
                     break
                 inputs[alias] = arr.astype(dt)
+            if inputs is not None:
+                for alias, dt in self.optional_inputs.items():
+                    if ('"%s"' % alias).encode() in body:
+                        arr = fast.parse(body, alias)
+                        if arr is None:
+                            inputs = None
+                            break
+                        inputs[alias] = arr.astype(dt)
             if inputs is not None:
                 out = self._run(inputs)
                 parts = []

@@ -174,13 +174,29 @@ class Supervisor:
             time.sleep(self.recovery_wait_secs)
 
     def _write_graph(self, sess) -> None:
+        """``graph.pbtxt`` in ``logdir``: the text form of the model's GraphDef (the same graph the event
+        file and ``saved_model.pb`` carry), as TF's Supervisor writes it (reference task.py:215-223)."""
+        text = ""
         try:
-            names = [v.name for v in sess.model.variables]
-        except Exception:
-            names = []
+            from tensorboard.compat.proto import graph_pb2
+            from .export.graph_def import build_graph_def, graph_def_text
+            g = graph_pb2.GraphDef()
+            tensors = None
+            try:
+                tensors = sess.snapshot()
+            except Exception:  # noqa: BLE001  (a session without snapshot(): model variables only)
+                tensors = None
+            build_graph_def(g, sess.model, tensors)
+            g.versions.producer = 134
+            text = graph_def_text(g)
+        except Exception:  # noqa: BLE001  (no protobuf runtime: fall back to a bare variable list)
+            try:
+                names = [v.name for v in sess.model.variables]
+            except Exception:  # noqa: BLE001
+                names = []
+            text = "".join('node {\n  name: "%s"\n  op: "VariableV2"\n}\n' % n for n in names)
         with open(os.path.join(self.logdir, "graph.pbtxt"), "w") as f:
-            for n in names:
-                f.write('node {\n  name: "%s"\n  op: "VariableV2"\n}\n' % n)
+            f.write(text)
 
     # ------------------------------------------------------------------ standard services
     def start_standard_services(self, sess) -> List[threading.Thread]:

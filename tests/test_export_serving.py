@@ -134,3 +134,157 @@ def test_wide_deep_numpy_predictor_assembles_shards_and_serves():
     assert np.isclose(out["prediction"][0, 0], 1 / (1 + np.exp(-logit)), rtol=1e-4)
     with pytest.raises(ValueError):
         p.predict({"keys": [[1]], "features": [[1.0, 2.0]]})
+
+
+def _tiny_wide_deep_variables(rows=11, world=1, seed=0):
+    rng = np.random.RandomState(seed)
+    cfg = dict(emb_rows=rows, emb_dim=128, slots=2, dense_in=3, dense_pad=64, h1=64, h2=64, h3=256, world=world)
+    K0 = 2 * 128 + 64
+    al = lambda v: (v + 255) // 256 * 256
+    P = al(al(al(al(al(al(al(64 * K0) + 64 * 64) + 256 * 64) + 64) + 64) + 256) + 256) + 8
+    flat = (rng.randn((P + 255) // 256 * 256) * 0.05).astype(np.float32)
+    emb = rng.randn(rows, 128).astype(np.float32)
+    wide = rng.randn(rows).astype(np.float32)
+    return {"embedding/part_0": emb, "wide_weights/part_0": wide, "dense_flat/part_0": flat}, cfg
+
+
+def test_wide_deep_ids_stay_exact_and_inexact_float32_ids_are_refused():
+    """Ids may come inside ``features`` (float64 end to end) or as the integer input ``ids``; a float32
+    array that can no longer tell neighbouring ids apart (>= 2**24) is an error, not a silent wrong row."""
+    from distributed_tensorflow_b200.models.wide_deep_serving import WideDeepPredictor
+    variables, cfg = _tiny_wide_deep_variables()
+    p = WideDeepPredictor(variables, cfg, device="cpu")
+    feats = np.array([[3, 10, 0.5, -1.0, 2.0]], np.float64)
+    a = p.predict({"keys": [[1]], "features": feats})["prediction"]
+    b = p.predict({"keys": [[1]], "features": feats[:, 2:], "ids": np.array([[3, 10]], np.int64)})["prediction"]
+    assert np.array_equal(a, b)
+    big = np.array([[2 ** 24 + 1, 10, 0.5, -1.0, 2.0]], np.float64)       # exact in float64: row (2**24 + 1) % 11
+    c = p.predict({"keys": [[1]], "features": big})["prediction"]
+    d = p.predict({"keys": [[1]], "features": big[:, 2:], "ids": np.array([[(2 ** 24 + 1) % 11, 10]])})["prediction"]
+    assert np.array_equal(c, d)
+    with pytest.raises(ValueError, match="2\\*\\*24"):
+        p.predict({"keys": [[1]], "features": big.astype(np.float32)})
+    with pytest.raises(ValueError, match="integers"):
+        p.predict({"keys": [[1]], "features": np.array([[3.5, 10, 0, 0, 0]])})
+
+
+def test_wide_deep_http_concurrent_posts_each_get_their_own_answer(tmp_path):
+    """Eight clients post different batches at once (ThreadingHTTPServer); every response must equal the
+    predictor's answer for that client's own inputs."""
+    import http.client
+    import threading
+    from distributed_tensorflow_b200.export.saved_model import DEFAULT_SERVING_SIGNATURE_DEF_KEY, SERVING, build_signature_def
+    from distributed_tensorflow_b200.models.wide_deep_serving import WideDeepPredictor
+    from distributed_tensorflow_b200.models.wide_deep_trainer import WideDeepServingSpec
+    variables, cfg = _tiny_wide_deep_variables(rows=64)
+    base = str(tmp_path / "wd")
+
+    class _Store:
+        model = WideDeepServingSpec(cfg)
+
+        def snapshot(self):
+            return dict(variables)
+
+    builder = SavedModelBuilder(os.path.join(base, "1"))
+    builder.add_meta_graph_and_variables(_Store(), [SERVING], signature_def_map={
+        DEFAULT_SERVING_SIGNATURE_DEF_KEY: build_signature_def(_Store.model)}, model=_Store.model)
+    builder.save()
+    ms = ModelServer(base, device="cpu")
+    ref = WideDeepPredictor(variables, cfg, device="cpu")
+    httpd = make_http_server(ms, "127.0.0.1", 0)
+    port = httpd.server_address[1]
+    t = threading.Thread(target=httpd.serve_forever, daemon=True)
+    t.start()
+    results, errors = {}, []
+
+    def client(i):
+        try:
+            rng = np.random.RandomState(100 + i)
+            n = 3 + i
+            feats = np.concatenate([rng.randint(0, 64, (n, 2)).astype(np.float64), rng.randn(n, 3)], axis=1)
+            body = json.dumps({"keys": [[i * 100 + j] for j in range(n)], "features": feats.tolist()})
+            for _ in range(5):
+                c = http.client.HTTPConnection("127.0.0.1", port, timeout=20)
+                c.request("POST", "/", body, {"Content-Type": "application/json"})
+                r = json.loads(c.getresponse().read())
+                c.close()
+                want = ref.predict({"keys": [[i * 100 + j] for j in range(n)], "features": feats})
+                assert r["keys"] == want["keys"].tolist()
+                assert np.allclose(np.array(r["prediction"]), want["prediction"], rtol=1e-5, atol=1e-6)
+            results[i] = True
+        except Exception as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    threads = [threading.Thread(target=client, args=(i,)) for i in range(8)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    httpd.shutdown()
+    httpd.server_close()
+    assert not errors and len(results) == 8, errors
+
+
+def _check_graph_is_closed(graph_def):
+    """Every input of every node (data or ^control, with or without :k) names a node of the graph."""
+    names = {n.name for n in graph_def.node}
+    assert len(names) == len(graph_def.node), "duplicate node names"
+    for n in graph_def.node:
+        for i in n.input:
+            src = i.lstrip("^").split(":")[0]
+            assert src in names, "%s reads %s which is not in the graph" % (n.name, i)
+    return {n.name: n for n in graph_def.node}
+
+
+def test_saved_model_graph_has_a_saver_subgraph_tf_could_run(tmp_path):
+    """The three names in saver_def exist in graph_def and are wired like TF's Saver(sharded=True):
+    save/Const is a string Const with a value, SaveV2/RestoreV2 carry the variable names, every variable has
+    a save/Assign fed by RestoreV2:i, restore_all depends on all of them, init covers every <v>/Assign."""
+    path = export_saved_model(_trained(), str(tmp_path / "sm"), 1)
+    mg = parse_saved_model_pb(os.path.join(path, "saved_model.pb"))[1][0]
+    nodes = _check_graph_is_closed(mg.graph_def)
+    sd = mg.saver_def
+    fname, save, restore = sd.filename_tensor_name, sd.save_tensor_name, sd.restore_op_name
+    assert fname.split(":")[0] in nodes and save.split(":")[0] in nodes and restore in nodes
+    const = nodes[fname.split(":")[0]]
+    assert const.op == "Const" and const.attr["dtype"].type == 7 and list(const.attr["value"].tensor.string_val) == [b"model"]
+    saved = ["bias", "bias/Adagrad", "global_step", "weight", "weight/Adagrad"]
+    assert [s.decode() for s in nodes["save/SaveV2/tensor_names"].attr["value"].tensor.string_val] == saved
+    assert list(nodes["save/SaveV2"].input[3:]) == saved
+    assert list(nodes["save/SaveV2"].attr["dtypes"].list.type) == [1, 1, 3, 1, 1]
+    assert nodes["save/RestoreV2"].input[0] == "save/Const"
+    assigns = [n for n in mg.graph_def.node if n.name.startswith("save/Assign")]
+    assert sorted(a.input[0] for a in assigns) == saved
+    assert {a.input[1].split(":")[0] for a in assigns} == {"save/RestoreV2"}
+    assert sorted(i for i in nodes["save/restore_shard"].input) == sorted("^" + a.name for a in assigns)
+    assert list(nodes[restore].input) == ["^save/restore_shard"]
+    assert "^save/SaveV2" in nodes["save/control_dependency"].input
+    assert nodes[save.split(":")[0]].op == "Identity" and "^save/MergeV2Checkpoints" in nodes[save.split(":")[0]].input
+    assert sorted(nodes["init"].input) == sorted("^%s/Assign" % v for v in saved)
+    # forward graph of reference task.py:137-139 and the tensors the signature names
+    assert nodes["add"].op == "Add" and list(nodes["add"].input) == ["Mul_1", "bias/read"]
+    assert nodes["Sum"].op == "Sum" and nodes["weight/initial_value"].attr["value"].tensor.float_val[0] == 0.0
+    for ti in list(mg.signature_def["serving_default"].inputs.values()) + list(mg.signature_def["serving_default"].outputs.values()):
+        assert ti.name.split(":")[0] in nodes
+
+
+def test_session_bundle_carries_a_signatures_proto(tmp_path):
+    """export.meta holds tensorflow.serving.Signatures (Any-wrapped, collection serving_signatures) with the
+    named generic signatures inputs{keys, X} / outputs{keys, predict} of reference task_supervisor.py:187-199."""
+    from tensorboard.compat.proto import meta_graph_pb2
+    from distributed_tensorflow_b200.export.session_bundle import decode_signatures, encode_signatures
+    p = export_session_bundle(_trained(), str(tmp_path / "legacy"), 3)
+    mg = meta_graph_pb2.MetaGraphDef()
+    mg.ParseFromString(open(os.path.join(p, "export.meta"), "rb").read())
+    anys = mg.collection_def["serving_signatures"].any_list.value
+    assert len(anys) == 1 and anys[0].type_url == "type.googleapis.com/tensorflow.serving.Signatures"
+    named = decode_signatures(anys[0].value)
+    assert named == {"inputs": {"keys": "Placeholder:0", "X": "Placeholder_1:0"},
+                     "outputs": {"keys": "Identity:0", "predict": "add:0"}}
+    # wire format spot check: Signatures.named_signatures is field 2, a map entry {1: key, 2: Signature{3: Generic}}
+    blob = encode_signatures({"inputs": {"X": "a:0"}})
+    assert blob == (bytes([0x12, 24, 0x0a, 6]) + b"inputs" + bytes([0x12, 14, 0x1a, 12, 0x0a, 10, 0x0a, 1]) + b"X"
+                    + bytes([0x12, 5, 0x0a, 3]) + b"a:0")
+    _check_graph_is_closed(mg.graph_def)
+    assert mg.collection_def["serving_graph"].any_list.value[0].type_url == "type.googleapis.com/tensorflow.GraphDef"
+    assert mg.saver_def.restore_op_name == "save/restore_all"
