@@ -313,14 +313,22 @@ struct dtfn_server {
   std::atomic<int> drop{0};
   Store store;
   std::thread accept_thread;
+  // live connections by id (fd numbers are reused by the process, ids are not); a handler that ends
+  // moves its id to `finished` so that the accept loop can join and forget its thread
+  struct Conn {
+    int fd = -1;
+    std::thread th;
+  };
   std::mutex conn_mu;
-  std::vector<std::thread> conn_threads;
-  std::vector<int> conn_fds;
+  std::map<long long, Conn> conns;
+  std::vector<long long> finished;
+  long long next_conn_id = 1;
   std::mutex join_mu;
   std::condition_variable join_cv;
   bool stopped = false;
 
-  void handle(int fd);
+  void handle(long long id, int fd);
+  void reap_finished();
   int dispatch(uint8_t op, Reader& r, Writer& w);
   void request_stop() {
     {
@@ -345,6 +353,16 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       size_t n;
       const char* data = r.bytes(&n);
       if (!r.ok) return -1;
+      // dtype and payload size come from the wire: a variable whose bytes do not match its declared
+      // shape would later be indexed past its end by the applies and the atomic step counter
+      if (dtype != DT_FLOAT && dtype != DT_INT32 && dtype != DT_INT64) return -11;
+      if (nd < 0 || nd > 8) return -1;
+      unsigned long long count = 1;
+      for (long long d : dims) {
+        if (d < 0 || (d > 0 && count > (1ull << 40) / static_cast<unsigned long long>(d))) return -1;
+        count *= static_cast<unsigned long long>(d);
+      }
+      if (count * (dtype == DT_INT64 ? 8u : 4u) != n) return -12;
       std::unique_lock<std::shared_mutex> l(store.mu);
       auto& p = store.vars[name];
       if (p && !overwrite) return 1;
@@ -433,12 +451,14 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       if (!step_name.empty()) {
         Var* sv = store.find(step_name);
         if (!sv) return -10;
-        if (sv->dtype == DT_INT64) {
+        if (sv->dtype == DT_INT64 && sv->data.size() >= 8) {
           auto* a = reinterpret_cast<std::atomic<int64_t>*>(sv->data.data());
           step = a->fetch_add(inc) + inc;
-        } else {
+        } else if (sv->dtype == DT_INT32 && sv->data.size() >= 4) {
           auto* a = reinterpret_cast<std::atomic<int32_t>*>(sv->data.data());
           step = a->fetch_add(static_cast<int32_t>(inc)) + static_cast<int32_t>(inc);
+        } else {
+          return -11;   // the step variable must be an integer scalar
         }
       }
       w.i64(step);
@@ -462,10 +482,10 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       Var* sv = store.find(name);
       if (!sv) return -10;
       int64_t out;
-      if (sv->dtype == DT_INT64) {
+      if (sv->dtype == DT_INT64 && sv->data.size() >= 8) {
         auto* a = reinterpret_cast<std::atomic<int64_t>*>(sv->data.data());
         out = a->fetch_add(delta) + delta;
-      } else if (sv->dtype == DT_INT32) {
+      } else if (sv->dtype == DT_INT32 && sv->data.size() >= 4) {
         auto* a = reinterpret_cast<std::atomic<int32_t>*>(sv->data.data());
         out = a->fetch_add(static_cast<int32_t>(delta)) + static_cast<int32_t>(delta);
       } else {
@@ -485,11 +505,19 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
       const std::string name = r.str();
       const int val = r.i32();
       if (!r.ok) return -1;
+      // optional trailing field: how long the server may hold the request while the queue is full; the
+      // client keeps it below its socket timeout, so no late reply can get out of step with a later request
+      int wait_ms = 500;
+      if (static_cast<size_t>(r.end - r.p) >= 4) wait_ms = r.i32();
       Queue* q = store.queue(name, 1 << 20, true);
       std::unique_lock<std::mutex> l(q->mu);
-      // bounded: block (briefly, in slices so shutdown is noticed) while the queue is full
-      while (q->capacity > 0 && static_cast<int>(q->items.size()) >= q->capacity && !stopping)
-        q->cv.wait_for(l, std::chrono::milliseconds(100));
+      const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(wait_ms);
+      while (q->capacity > 0 && static_cast<int>(q->items.size()) >= q->capacity) {
+        if (stopping) return -2;
+        if (q->cv.wait_until(l, deadline) == std::cv_status::timeout &&
+            static_cast<int>(q->items.size()) >= q->capacity)
+          return -2;   // still full: the client retries
+      }
       q->items.push_back(val);
       q->cv.notify_all();
       return 0;
@@ -541,7 +569,23 @@ int dtfn_server::dispatch(uint8_t op, Reader& r, Writer& w) {
   }
 }
 
-void dtfn_server::handle(int fd) {
+void dtfn_server::reap_finished() {
+  std::vector<std::thread> done;
+  {
+    std::lock_guard<std::mutex> l(conn_mu);
+    for (long long id : finished) {
+      auto it = conns.find(id);
+      if (it == conns.end()) continue;
+      done.push_back(std::move(it->second.th));
+      conns.erase(it);
+    }
+    finished.clear();
+  }
+  for (auto& t : done)
+    if (t.joinable()) t.join();
+}
+
+void dtfn_server::handle(long long id, int fd) {
   tune_socket(fd);
   std::string buf;   // only ever grows: resize() would zero-fill megabytes per request otherwise
   for (;;) {
@@ -564,6 +608,14 @@ void dtfn_server::handle(int fd) {
     memcpy(hdr + 4, &st, 4);
     if (!send_frame(fd, hdr, 8, w.s)) break;
     if (op == OP_SHUTDOWN) break;
+  }
+  {
+    // forget the descriptor before closing it: stop() must never shutdown() a number that the process
+    // has meanwhile handed to another socket
+    std::lock_guard<std::mutex> l(conn_mu);
+    auto it = conns.find(id);
+    if (it != conns.end()) it->second.fd = -1;
+    finished.push_back(id);
   }
   ::shutdown(fd, SHUT_RDWR);
   ::close(fd);
@@ -610,9 +662,12 @@ dtfn_server* dtfn_server_start(const char* host, int port) {
       if (pr <= 0) continue;
       const int c = ::accept(s->listen_fd, nullptr, nullptr);
       if (c < 0) continue;
+      s->reap_finished();
       std::lock_guard<std::mutex> l(s->conn_mu);
-      s->conn_fds.push_back(c);
-      s->conn_threads.emplace_back([s, c] { s->handle(c); });
+      const long long id = s->next_conn_id++;
+      auto& conn = s->conns[id];
+      conn.fd = c;
+      conn.th = std::thread([s, id, c] { s->handle(id, c); });
     }
   });
   return s;
@@ -631,14 +686,20 @@ void dtfn_server_stop(dtfn_server* s) {
   ::close(s->listen_fd);
   {
     std::lock_guard<std::mutex> l(s->conn_mu);
-    for (int fd : s->conn_fds) ::shutdown(fd, SHUT_RDWR);
+    for (auto& kv : s->conns)
+      if (kv.second.fd >= 0) ::shutdown(kv.second.fd, SHUT_RDWR);
   }
   // wake any handler blocked in a queue wait
   {
     std::lock_guard<std::mutex> l(s->store.qmu);
     for (auto& kv : s->store.queues) kv.second->cv.notify_all();
   }
-  for (auto& t : s->conn_threads)
+  std::vector<std::thread> all;
+  {
+    std::lock_guard<std::mutex> l(s->conn_mu);
+    for (auto& kv : s->conns) all.push_back(std::move(kv.second.th));
+  }
+  for (auto& t : all)
     if (t.joinable()) t.join();
   delete s;
 }
@@ -654,12 +715,26 @@ long long dtfn_server_num_variables(const dtfn_server* s) {
 }  // extern "C"
 
 // ------------------------------------------------------------------------------- client
+static int open_client_socket(const char* host, int port, int timeout_ms);
+
 struct dtfn_client {
   int fd = -1;
   std::string host;
   int port = 0;
+  int timeout_ms = 0;
   std::mutex mu;
   std::string resp;
+
+  // A request that failed in transit may still be answered later (a slow SAVE, an ENQUEUE held on a
+  // full queue): that late reply would be read as the answer to the next request.  So the socket of a
+  // failed exchange is never reused -- it is closed, and the next call starts on a fresh connection.
+  void poison() {
+    if (fd >= 0) {
+      ::shutdown(fd, SHUT_RDWR);
+      ::close(fd);
+    }
+    fd = -1;
+  }
 
   // sends one request and receives the response payload into `resp`; returns status or <= -100 on
   // transport failure
@@ -668,29 +743,66 @@ struct dtfn_client {
     const uint32_t len = static_cast<uint32_t>(1 + w.s.size());
     memcpy(hdr, &len, 4);
     hdr[4] = static_cast<char>(op);
+    if (fd < 0) {
+      fd = open_client_socket(host.c_str(), port, timeout_ms);
+      if (fd < 0) return -100;   // error text set by open_client_socket
+    }
     if (!send_frame(fd, hdr, 5, w.s)) {
       set_error("client: send to %s:%d failed: %s", host.c_str(), port, strerror(errno));
+      poison();
       return -100;
     }
     uint32_t rlen;
     if (!recv_all(fd, &rlen, 4) || rlen < 4 || rlen > (1u << 30)) {
       set_error("client: no response from %s:%d (peer closed or timed out)", host.c_str(), port);
+      poison();
       return -101;
     }
     int32_t status;
     if (!recv_all(fd, &status, 4)) {
       set_error("client: truncated response from %s:%d", host.c_str(), port);
+      poison();
       return -101;
     }
     resp.resize(rlen - 4);
     if (rlen > 4 && !recv_all(fd, &resp[0], rlen - 4)) {
       set_error("client: truncated response from %s:%d", host.c_str(), port);
+      poison();
       return -101;
     }
     if (status < 0 && status > -100) set_error("client: server returned status %d for op %d", status, (int)op);
     return status;
   }
 };
+
+static void set_sock_timeout(int fd, int timeout_ms);
+static int open_client_socket(const char* host, int port, int timeout_ms) {
+  addrinfo hints{}, *res = nullptr;
+  hints.ai_family = AF_INET;
+  hints.ai_socktype = SOCK_STREAM;
+  char portstr[16];
+  snprintf(portstr, sizeof(portstr), "%d", port);
+  if (getaddrinfo(host, portstr, &hints, &res) != 0 || !res) {
+    set_error("client: cannot resolve %s", host);
+    return -1;
+  }
+  const int fd = ::socket(AF_INET, SOCK_STREAM, 0);
+  if (fd < 0) {
+    freeaddrinfo(res);
+    set_error("client: socket() failed");
+    return -1;
+  }
+  if (timeout_ms > 0) set_sock_timeout(fd, timeout_ms);
+  const int rc = ::connect(fd, res->ai_addr, res->ai_addrlen);
+  freeaddrinfo(res);
+  if (rc != 0) {
+    set_error("client: connect to %s:%d failed: %s", host, port, strerror(errno));
+    ::close(fd);
+    return -1;
+  }
+  tune_socket(fd);
+  return fd;
+}
 
 static void set_sock_timeout(int fd, int timeout_ms) {
   timeval tv{};
@@ -704,45 +816,27 @@ extern "C" {
 
 dtfn_client* dtfn_client_connect(const char* host, int port, int timeout_ms) {
   if (host == nullptr || host[0] == '\0' || strcmp(host, "localhost") == 0) host = "127.0.0.1";
-  addrinfo hints{}, *res = nullptr;
-  hints.ai_family = AF_INET;
-  hints.ai_socktype = SOCK_STREAM;
-  char portstr[16];
-  snprintf(portstr, sizeof(portstr), "%d", port);
-  if (getaddrinfo(host, portstr, &hints, &res) != 0 || !res) {
-    set_error("client: cannot resolve %s", host);
-    return nullptr;
-  }
-  const int fd = ::socket(AF_INET, SOCK_STREAM, 0);
-  if (fd < 0) {
-    freeaddrinfo(res);
-    set_error("client: socket() failed");
-    return nullptr;
-  }
-  if (timeout_ms > 0) set_sock_timeout(fd, timeout_ms);
-  const int rc = ::connect(fd, res->ai_addr, res->ai_addrlen);
-  freeaddrinfo(res);
-  if (rc != 0) {
-    set_error("client: connect to %s:%d failed: %s", host, port, strerror(errno));
-    ::close(fd);
-    return nullptr;
-  }
-  tune_socket(fd);
+  const int fd = open_client_socket(host, port, timeout_ms);
+  if (fd < 0) return nullptr;
   auto* c = new dtfn_client();
   c->fd = fd;
   c->host = host;
   c->port = port;
+  c->timeout_ms = timeout_ms;
   return c;
 }
 
 void dtfn_client_close(dtfn_client* c) {
   if (!c) return;
-  ::shutdown(c->fd, SHUT_RDWR);
-  ::close(c->fd);
+  c->poison();
   delete c;
 }
 
-void dtfn_client_set_timeout(dtfn_client* c, int timeout_ms) { set_sock_timeout(c->fd, timeout_ms); }
+void dtfn_client_set_timeout(dtfn_client* c, int timeout_ms) {
+  std::lock_guard<std::mutex> l(c->mu);
+  c->timeout_ms = timeout_ms;
+  if (c->fd >= 0) set_sock_timeout(c->fd, timeout_ms);
+}
 
 int dtfn_client_ping(dtfn_client* c) {
   std::lock_guard<std::mutex> l(c->mu);
@@ -882,11 +976,25 @@ int dtfn_client_queue_create(dtfn_client* c, const char* name, int capacity) {
 }
 
 int dtfn_client_enqueue(dtfn_client* c, const char* name, int value) {
-  std::lock_guard<std::mutex> l(c->mu);
-  Writer w;
-  w.str(name);
-  w.i32(value);
-  return c->call(OP_ENQUEUE, w);
+  // a full bounded queue holds the request for at most `slice` ms per attempt (below the socket
+  // timeout); -2 = still full, ask again, up to the connection's timeout over all attempts
+  const int budget_ms = c->timeout_ms > 0 ? c->timeout_ms : 30000;
+  const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(budget_ms);
+  for (;;) {
+    const auto left =
+        std::chrono::duration_cast<std::chrono::milliseconds>(deadline - std::chrono::steady_clock::now()).count();
+    if (left <= 0) {
+      set_error("client: queue '%s' on %s:%d stayed full for %d ms", name, c->host.c_str(), c->port, budget_ms);
+      return -2;
+    }
+    std::lock_guard<std::mutex> l(c->mu);
+    Writer w;
+    w.str(name);
+    w.i32(value);
+    w.i32(static_cast<int>(std::min<long long>(500, left)));
+    const int st = c->call(OP_ENQUEUE, w);
+    if (st != -2) return st;
+  }
 }
 
 int dtfn_client_dequeue(dtfn_client* c, const char* name, int* value, int timeout_ms) {

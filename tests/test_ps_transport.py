@@ -172,3 +172,72 @@ def test_ps_session_two_ps_tasks_round_robin_and_convergence():
         sess.close()
     finally:
         s0.stop(), s1.stop()
+
+
+def test_client_recovers_on_a_fresh_connection_after_a_lost_exchange(ps):
+    """A request that got no answer in time must not leave the socket one reply out of step: the client
+    drops that connection and the next call runs on a new one, with its own reply."""
+    srv, addr = ps
+    c = PSClient(addr, timeout_ms=400)
+    c.init_var("w", np.array([1.0, 2.0], np.float32))
+    c.init_var("global_step", np.array(5, np.int32))
+    srv.inject_drop(1)                                                         # the server vanishes mid-request
+    with pytest.raises(ConnectionError):
+        c.pull("w")
+    # same client object: reconnects, and replies line up with requests again
+    assert c.pull("w").tolist() == [1.0, 2.0]
+    assert c.assign_add("global_step", 2) == 7
+    assert sorted(c.list()) == ["global_step", "w"]
+    c.close()
+
+
+def test_full_bounded_queue_holds_an_enqueue_only_for_the_client_timeout(ps):
+    _, addr = ps
+    a = PSClient(addr, timeout_ms=700)
+    a.queue_create("q", 1)
+    a.enqueue("q", 1)
+    t0 = time.time()
+    with pytest.raises(_native.NativeError):
+        a.enqueue("q", 2)                                                      # full: gives up after ~0.7 s
+    assert 0.5 < time.time() - t0 < 3.0
+    assert a.dequeue("q", timeout_ms=500) == 1                                 # connection still in step
+    a.enqueue("q", 3)
+    assert a.dequeue("q", timeout_ms=500) == 3
+    a.close()
+
+
+def test_init_var_rejects_sizes_that_do_not_match_the_shape_and_non_integer_step(ps):
+    import ctypes as C
+    _, addr = ps
+    c = PSClient(addr)
+    L = _native.lib()
+    data = np.zeros(3, np.float32)
+    dims = (C.c_longlong * 1)(5)                                               # claims 5 floats, sends 3
+    rc = L.dtfn_client_init_var(c._h, b"bad", 1, 1, dims, data.ctypes.data_as(C.c_void_p), data.nbytes, 1)
+    assert rc == -12
+    rc = L.dtfn_client_init_var(c._h, b"bad", 19, 1, (C.c_longlong * 1)(3), data.ctypes.data_as(C.c_void_p), data.nbytes, 1)
+    assert rc == -11                                                           # DT_HALF is not a ps dtype
+    c.init_var("fstep", np.array(0.0, np.float32))
+    with pytest.raises(_native.NativeError):
+        c.assign_add("fstep", 1)
+    with pytest.raises(_native.NativeError):
+        c.push_pull([], [], 0, 0.1, "fstep")
+    c.close()
+
+
+def test_many_short_connections_are_reaped_and_stop_is_clean():
+    srv = Server(ClusterSpec({"ps": ["127.0.0.1:0"]}), "ps", 0)
+    addr = "127.0.0.1:%d" % srv.port
+    for i in range(50):
+        c = PSClient(addr)
+        c.ping()
+        c.close()
+    keep = PSClient(addr)
+    keep.init_var("w", np.zeros(1, np.float32))
+    other = Server(ClusterSpec({"ps": ["127.0.0.1:0"]}), "ps", 0)              # its sockets may reuse freed fd numbers
+    oc = PSClient("127.0.0.1:%d" % other.port)
+    srv.stop()                                                                 # must not touch `other`'s descriptors
+    oc.ping()
+    oc.close()
+    other.stop()
+    keep.close()
