@@ -215,11 +215,19 @@ def MonitoredTrainingSession(master: str = "", is_chief: bool = True, checkpoint
     if is_chief:
         sess = session_factory(master)
         ckpt = latest_checkpoint(checkpoint_dir) if checkpoint_dir else None
-        sess.run_init()
-        if ckpt is not None:
+        if ckpt is None:
+            sess.run_init()
+        else:
+            # restore without init: live ps state is not reset and readiness is published last
+            if hasattr(sess, "begin_restore"):
+                sess.begin_restore()
             sv = saver or next((h.saver for h in all_hooks if isinstance(h, CheckpointSaverHook)), Saver())
             sv.recover_last_checkpoints(checkpoint_dir)
             sv.restore(sess, ckpt)
+            if hasattr(sess, "end_restore"):
+                sess.end_restore()
+            elif not sess.is_ready():
+                sess.run_init()
             if hasattr(sess, "refresh"):
                 sess.refresh()
         if not sess.is_ready():

@@ -40,6 +40,14 @@ class LocalSession:
     def is_ready(self) -> bool:
         return all(v.name in self.store for v in self.model.variables)
 
+    def end_restore(self) -> None:
+        """After a restore: variables (and slots) the checkpoint did not hold get their initial value."""
+        for k, v in self.model.initial_values().items():
+            self.store.setdefault(k, v)
+        if self.optimizer is not None:
+            for n in self.model.trainable_names():
+                self.optimizer.ensure_slots(self.store, n)
+
     def close(self) -> None:
         pass
 
@@ -201,15 +209,37 @@ class PSSession:
             c.close()
 
     # -- lifecycle ---------------------------------------------------------------------------
-    def run_init(self) -> None:
-        """``sess.run(init_op)``: (re)create every model variable on its ps task (chief only)."""
+    READY_MARKER = "_dtf_ready"   # ps-side flag written last by the chief; never part of a checkpoint
+
+    def run_init(self, overwrite: bool = True) -> None:
+        """``sess.run(init_op)``: (re)create every model variable on its ps task (chief only), then
+        publish readiness.  ``overwrite=False`` only fills in variables that do not exist yet."""
         for v in self.model.variables:
-            self.clients[self.setter.task_of(v.name)].init_var(v.name, v.initial, overwrite=True)
+            self.clients[self.setter.task_of(v.name)].init_var(v.name, v.initial, overwrite=overwrite)
+        self._set_ready(1)
         self.refresh()
 
+    def _set_ready(self, value: int) -> None:
+        for c in self.clients:
+            c.init_var(self.READY_MARKER, np.array(value, np.int32), overwrite=True)
+
+    def begin_restore(self) -> None:
+        """Chief, before assigning checkpoint tensors: withdraw readiness so that workers that poll
+        ``is_ready`` do not start on half-restored state.  Live variables are left alone (TF's
+        Supervisor restores without running init_op)."""
+        self._set_ready(0)
+
+    def end_restore(self) -> None:
+        """Variables the checkpoint did not hold get their initial value; readiness is published last."""
+        self.run_init(overwrite=False)
+
     def is_ready(self) -> bool:
-        """``report_uninitialized_variables`` is empty: every model variable exists on its ps."""
+        """``report_uninitialized_variables`` is empty: every model variable exists on its ps and the
+        chief has finished initialising or restoring (ready marker set on every ps task)."""
         try:
+            for c in self.clients:
+                if c.var_info(self.READY_MARKER) is None or int(c.pull(self.READY_MARKER)) != 1:
+                    return False
             for v in self.model.variables:
                 if self.clients[self.setter.task_of(v.name)].var_info(v.name) is None:
                     return False
@@ -253,7 +283,7 @@ class PSSession:
         out: Dict[str, np.ndarray] = {}
         for c in self.clients:
             for n in c.list():
-                if n not in out:
+                if n not in out and n != self.READY_MARKER:
                     out[n] = c.pull(n)
         return out
 
@@ -274,7 +304,7 @@ class PSSession:
         prefixes = []
         for i, c in enumerate(self.clients):
             names = c.list()
-            exclude = [n for n in names if n in seen or (var_list is not None and n not in var_list)]
+            exclude = [n for n in names if n in seen or n == self.READY_MARKER or (var_list is not None and n not in var_list)]
             seen.update(names)
             p = "%s-%05d" % (tmp_prefix, i)
             c.save(p, exclude)

@@ -135,10 +135,17 @@ class Supervisor:
             sess = self.session_factory(master)
             ckpt = latest_checkpoint(self.logdir) if (self.logdir and self.saver is not None) else None
             if ckpt is not None:
-                # model variables must exist before tensors can be assigned onto their ps tasks
-                sess.run_init()
+                # like TF's SessionManager: restore WITHOUT running init_op -- assign() creates what is
+                # missing, live variables of a running job are not reset, and readiness is only
+                # published once the restore is complete
+                if hasattr(sess, "begin_restore"):
+                    sess.begin_restore()
                 self.saver.recover_last_checkpoints(self.logdir)
                 self.saver.restore(sess, ckpt)
+                if hasattr(sess, "end_restore"):
+                    sess.end_restore()
+                else:
+                    sess.run_init() if not sess.is_ready() else None
                 if hasattr(sess, "refresh"):
                     sess.refresh()
                 self.restored_from = ckpt

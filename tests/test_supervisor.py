@@ -130,3 +130,48 @@ def test_coordinator_and_looper():
     assert coord.wait_for_stop(2)
     with pytest.raises(ZeroDivisionError):
         coord.join()
+
+
+def test_chief_restart_restores_without_resetting_live_ps_state_and_publishes_readiness_last(tmp_path):
+    """A chief that comes back while the job is running must not run init_op over live variables
+    (TF's Supervisor restores instead), must keep optimizer slots consistent with the checkpoint, and
+    workers polling is_ready() must not see 'ready' before the restore has finished."""
+    import numpy as np
+    from distributed_tensorflow_b200.cluster import ClusterSpec, Server
+    from distributed_tensorflow_b200.models.linear import LinearModel
+    from distributed_tensorflow_b200.optim import get_optimizer
+    from distributed_tensorflow_b200.session import PSSession
+    cluster = ClusterSpec({"ps": ["127.0.0.1:0"], "master": ["127.0.0.1:0"]})
+    srv = Server(cluster, "ps", 0)
+    cluster = ClusterSpec({"ps": ["127.0.0.1:%d" % srv.port], "master": ["127.0.0.1:0"]})
+    logdir = str(tmp_path / "ckpt")
+    factory = lambda master: PSSession(LinearModel(), get_optimizer("adagrad", 0.1), cluster, connect_retry_secs=5)
+    sv = Supervisor(is_chief=True, logdir=logdir, save_model_secs=0, session_factory=factory, recovery_wait_secs=0.05)
+    sess = sv.prepare_or_wait_for_session("", start_standard_services=False)
+    for _ in range(5):
+        sess.train_step(0.5, 11.0)
+    sv.saver.save(sess, sv.save_path, global_step=sess.global_step())
+    saved_w = float(sess.value("weight"))
+    for _ in range(3):                                     # the job keeps training after the checkpoint
+        sess.train_step(0.5, 11.0)
+    seen = []
+    orig_assign = PSSession.assign
+
+    def spying_assign(self, name, value):                  # what a polling worker would see mid-restore
+        seen.append(factory("").is_ready())
+        return orig_assign(self, name, value)
+
+    PSSession.assign = spying_assign
+    try:
+        sv2 = Supervisor(is_chief=True, logdir=logdir, save_model_secs=0, session_factory=factory)
+        sess2 = sv2.prepare_or_wait_for_session("", start_standard_services=False)
+    finally:
+        PSSession.assign = orig_assign
+    assert sv2.restored_from is not None and seen and not any(seen)      # not ready while tensors were being assigned
+    assert sess2.is_ready()
+    assert float(sess2.value("weight")) == saved_w and sess2.global_step() == 5
+    assert "_dtf_ready" not in sess2.snapshot()
+    worker = factory("")
+    assert worker.is_ready()
+    worker.close(), sess.close(), sess2.close()
+    srv.stop()
