@@ -38,7 +38,7 @@ struct OptConst {
 struct StepState {
   long long step;          // global_step of this shard (K7: folded into the apply)
   unsigned int epoch;      // barrier generation
-  unsigned int pad;
+  unsigned int error;      // != 0: a device barrier gave up waiting for rank (error - 1); sticky, read by the host
   OptConst oc;
 };
 
@@ -673,7 +673,8 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
 // Device-side barrier over the signal pads (one 64-byte line per source on every rank).  Thread r
 // optionally publishes how many mailbox entries this rank pushed to rank r, then release-stores
 // `epoch` into rank r's pad and acquire-spins on its own pad until rank r has done the same.
-__global__ void wd_barrier_kernel(PeerTable pt, SlabLayout sl, StepState* stp, const unsigned int* publish_cnt) {
+__global__ void wd_barrier_kernel(PeerTable pt, SlabLayout sl, StepState* stp, const unsigned int* publish_cnt,
+                                  unsigned long long timeout_ns) {
   __shared__ unsigned int s_epoch;
   if (threadIdx.x == 0) {
     s_epoch = stp->epoch + 1;
@@ -688,10 +689,25 @@ __global__ void wd_barrier_kernel(PeerTable pt, SlabLayout sl, StepState* stp, c
   unsigned int* remote = reinterpret_cast<unsigned int*>(pt.slab[r] + sl.signal) + pt.rank * 16;
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
   const unsigned int* mine = reinterpret_cast<const unsigned int*>(pt.slab[pt.rank] + sl.signal) + r * 16;
+  // Bounded wait: a rank that died or fell out of the job never signals.  After
+  // `timeout_ns` the waiter records which rank it missed in StepState::error and gives up; once the flag
+  // is set every later barrier returns at once, so the host, which polls the flag (dtf_wd_check_error),
+  // gets control back within one timeout instead of a silent hang of all ranks.
+  if (*reinterpret_cast<volatile unsigned int*>(&stp->error) != 0u) return;
   unsigned int v;
-  do {
+  unsigned long long t0 = 0;
+  for (unsigned int spin = 0;; ++spin) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-  } while (static_cast<int>(v - epoch) < 0);
+    if (static_cast<int>(v - epoch) >= 0) break;
+    if (timeout_ns != 0ull && (spin & 255u) == 255u) {
+      const unsigned long long t = globaltimer_ns();
+      if (t0 == 0ull) t0 = t;
+      else if (t - t0 > timeout_ns) {
+        atomicCAS(&stp->error, 0u, static_cast<unsigned int>(r) + 1u);
+        break;
+      }
+    }
+  }
 }
 
 // single-rank stand-in for the publish half of the barrier (counts stay local)

@@ -850,6 +850,37 @@ int dtf_wd_step_compute(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   return compute_impl(p, ids, dense_raw, labels, reinterpret_cast<cudaStream_t>(stream_), false);
 }
 
+// How long a device barrier waits for a peer before it records an error (DTF_BARRIER_TIMEOUT_MS, default
+// 30 s like --ps_timeout_ms; 0 = wait forever).  dtf_wd_set_barrier_timeout_ms overrides the environment.
+static long long g_barrier_timeout_ms = -1;
+static unsigned long long barrier_timeout_ns() {
+  if (g_barrier_timeout_ms < 0) {
+    const char* e = getenv("DTF_BARRIER_TIMEOUT_MS");
+    g_barrier_timeout_ms = e ? atoll(e) : 30000;
+    if (g_barrier_timeout_ms < 0) g_barrier_timeout_ms = 0;
+  }
+  return static_cast<unsigned long long>(g_barrier_timeout_ms) * 1000000ull;
+}
+void dtf_wd_set_barrier_timeout_ms(long long ms) { g_barrier_timeout_ms = ms < 0 ? 0 : ms; }
+
+// 0 = healthy; r + 1 = a device barrier of this plan stopped waiting for rank r (dead or stalled peer).
+// Reads the flag with a copy on a private stream, so the training streams are not synchronised.
+int dtf_wd_check_error(dtf_wd_plan* p) {
+  static thread_local cudaStream_t probe = nullptr;
+  if (probe == nullptr && cudaStreamCreateWithFlags(&probe, cudaStreamNonBlocking) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  unsigned int v = 0;
+  if (cudaMemcpyAsync(&v, &p->state->error, sizeof(v), cudaMemcpyDeviceToHost, probe) != cudaSuccess ||
+      cudaStreamSynchronize(probe) != cudaSuccess) {
+    set_error("dtf_wd_check_error: %s", cudaGetErrorString(cudaGetLastError()));
+    return -1;
+  }
+  if (v != 0) set_error("device barrier timed out waiting for rank %u (peer dead or stalled)", v - 1);
+  return static_cast<int>(v);
+}
+
 // cross-rank barrier on the device (no-op publish for a single rank)
 int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
@@ -860,7 +891,8 @@ int dtf_wd_barrier(dtf_wd_plan* p, int publish_counts, void* stream_) {
       count_launch();
     }
   } else {
-    wd_barrier_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->state, publish_counts ? p->cnt : nullptr);
+    wd_barrier_kernel<<<1, kMaxWorld, 0, st>>>(p->pt, p->sl, p->state, publish_counts ? p->cnt : nullptr,
+                                               barrier_timeout_ns());
     count_launch();
   }
   mark(p, st, "barrier");

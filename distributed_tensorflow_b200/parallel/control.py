@@ -87,11 +87,13 @@ class TransportGroup:
 
     # -- collectives (torch.distributed call shapes) ------------------------------------------------
     def barrier(self) -> None:
-        """Rank 0 collects one token per peer, then releases them.  Queue names are reused: a rank cannot
-        enter the next barrier before it was released from this one, so tokens never mix."""
+        """Rank 0 collects one token per peer, then releases them.  The release queue alternates between two
+        names: a rank that is already in barrier k+1 must not take a release token of barrier k that a
+        slower peer is still waiting for; by barrier k+2 every token of barrier k has been taken."""
         if self.world == 1:
             return
-        q_in, q_out = "%s/barrier/in" % self.tag, "%s/barrier/out" % self.tag
+        self._nbar = getattr(self, "_nbar", 0) + 1
+        q_in, q_out = "%s/barrier/in" % self.tag, "%s/barrier/out%d" % (self.tag, self._nbar & 1)
         if self.rank == 0:
             for _ in range(self.world - 1):
                 self._take(q_in)

@@ -189,6 +189,13 @@ int dtf_wd_broadcast_dense(dtf_wd_plan*, void* stream);
 int dtf_wd_refresh_embedding(dtf_wd_plan*, void* stream);
 int dtf_wd_step_compute(dtf_wd_plan*, const int* ids, const float* dense, const float* labels, void* stream);
 int dtf_wd_barrier(dtf_wd_plan*, int publish_counts, void* stream);
+/* Failure detection on the device (the reference's workers hang in gRPC when a ps dies, SURVEY.md 5.3;
+ * here a dead peer must not hang the survivors): a device barrier waits at most this long for a peer
+ * (default 30 000 ms, env DTF_BARRIER_TIMEOUT_MS, 0 = forever), then records the missing rank.
+ * dtf_wd_check_error: 0 healthy, r + 1 = gave up on rank r (sticky), < 0 CUDA error; does not
+ * synchronise the training streams. */
+void dtf_wd_set_barrier_timeout_ms(long long ms);
+int dtf_wd_check_error(dtf_wd_plan*);
 int dtf_wd_step_apply(dtf_wd_plan*, void* stream);
 int dtf_wd_step(dtf_wd_plan*, const int* ids, const float* dense, const float* labels, void* stream);
 int dtf_wd_predict(dtf_wd_plan*, const int* ids, const float* dense, int n /* <= batch */, void* stream);
