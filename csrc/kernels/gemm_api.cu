@@ -97,8 +97,10 @@ extern "C" int dtf_pull_gemm_bf16(const unsigned long long* row_src, const void*
                                   void* a_buf, const void* W, long long ldw, const float* bias, void* H,
                                   long long ldh, void* mask_out, long long ldmask, int M, int N, int relu,
                                   void* scratch, void* stream) {
-  if (M <= 0 || N <= 0 || slots <= 0 || dense_cols < 0 || (dense_cols % 64) != 0) {
-    set_error("dtf_pull_gemm_bf16: bad shape M=%d N=%d slots=%d dense_cols=%d (dense_cols multiple of 64)", M, N,
+  // the gather warps move the dense block as ONE 64-column chunk per row (gemm_sm100.cuh): wider blocks would
+  // leave rows 8..15 of every slice unwritten, so only "no dense block" and "64 columns" are accepted
+  if (M <= 0 || N <= 0 || slots <= 0 || (dense_cols != 0 && dense_cols != 64)) {
+    set_error("dtf_pull_gemm_bf16: bad shape M=%d N=%d slots=%d dense_cols=%d (dense_cols must be 0 or 64)", M, N,
               slots, dense_cols);
     return -2;
   }

@@ -73,8 +73,8 @@ extern "C" int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, con
                                           int dense_cols, void* a_buf, const void* W, long long ldw,
                                           const float* bias, void* H, long long ldh, void* mask_out,
                                           long long ldmask, int M, int N, int relu, void* stream) {
-  if (M <= 0 || N <= 0 || slots <= 0 || dense_cols < 0 || (dense_cols % 64) != 0) {
-    set_error("dtf_pull_gemm_bf16_noalloc: bad shape M=%d N=%d slots=%d dense_cols=%d (dense_cols multiple of 64)",
+  if (M <= 0 || N <= 0 || slots <= 0 || (dense_cols != 0 && dense_cols != 64)) {
+    set_error("dtf_pull_gemm_bf16_noalloc: bad shape M=%d N=%d slots=%d dense_cols=%d (dense_cols must be 0 or 64)",
               M, N, slots, dense_cols);
     return -2;
   }
@@ -111,5 +111,6 @@ extern "C" int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, con
   a.chunk_counter = scratch;
   a.tile_flags = reinterpret_cast<unsigned long long*>(scratch + 64);
   a.bn = (N % 256 == 0 || N > 512) ? 256 : 128;
+  a.pair = pair_eligible(a, a.bn);   // same tile shape choice as dtf_pull_gemm_bf16 (CTA pairs where the shape allows)
   return launch_gemm_gather(a);
 }

@@ -11,12 +11,13 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "wd_optim.cuh"
+
 namespace dtf {
 
 constexpr int kMaxWorld = 16;
 constexpr int kEmbDim = 128;  // one embedding row = 128 bf16 = 256 B = two 128-byte swizzle rows
 
-enum WdOptimizer : int { WD_SGD = 0, WD_ADAGRAD = 2, WD_ADAM = 3 };  // ids shared with dtf_native.h
 
 struct PeerTable {
   uint8_t* slab[kMaxWorld];

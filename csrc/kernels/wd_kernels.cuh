@@ -28,11 +28,6 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-struct OptConst {
-  float lr;       // SGD / Adagrad step; for Adam: lr * sqrt(1 - b2^t) / (1 - b1^t)
-  float beta1, beta2, eps;
-};
-
 // Device-resident step state so that a captured CUDA graph of the step stays valid across replays:
 // the step counter, the per-step optimizer constants and the barrier epoch all live in HBM.
 struct StepState {
@@ -52,20 +47,6 @@ __global__ void wd_tick_kernel(StepState* st, float base_lr, int opt) {
     oc.lr = static_cast<float>(base_lr * sqrt(1.0 - b2t) / (1.0 - b1t));
   }
   st->oc = oc;
-}
-
-template <int OPT>
-__device__ __forceinline__ void opt_update(float& w, float g, float& s1, float& s2, const OptConst& c) {
-  if (OPT == WD_SGD) {
-    w -= c.lr * g;
-  } else if (OPT == WD_ADAGRAD) {
-    s1 += g * g;
-    w -= c.lr * g * rsqrtf(s1);
-  } else {
-    s1 = c.beta1 * s1 + (1.f - c.beta1) * g;
-    s2 = c.beta2 * s2 + (1.f - c.beta2) * g * g;
-    w -= c.lr * s1 / (sqrtf(s2) + c.eps);
-  }
 }
 
 // ------------------------------------------------------------------------------------------ init
@@ -413,12 +394,12 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
       raw[u] = *reinterpret_cast<const uint2*>(mv.payload + e[u] * kEmbDim + lane * 4);
       w[u] = *reinterpret_cast<float4*>(master + o[u]);
       if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
-      if (OPT == WD_ADAM) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
+      if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
       if (lane == 0) {
         dlv[u] = mv.dl[e[u]];
         ww[u] = wide[row[u]];
         if (OPT != WD_SGD) wa[u] = wide_s1[row[u]];
-        if (OPT == WD_ADAM) wv[u] = wide_s2[row[u]];
+        if (opt_has_slot2(OPT)) wv[u] = wide_s2[row[u]];
       }
     }
 #pragma unroll
@@ -432,7 +413,7 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
       opt_update<OPT>(w[u].w, gb.y, a[u].w, v[u].w, oc);
       *reinterpret_cast<float4*>(master + o[u]) = w[u];
       if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o[u]) = a[u];
-      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
+      if (opt_has_slot2(OPT)) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
       uint2 pk;
       pk.x = pack_bf16x2(w[u].x, w[u].y);
       pk.y = pack_bf16x2(w[u].z, w[u].w);
@@ -441,7 +422,7 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
         opt_update<OPT>(ww[u], dlv[u], wa[u], wv[u], oc);
         wide[row[u]] = ww[u];
         if (OPT != WD_SGD) wide_s1[row[u]] = wa[u];
-        if (OPT == WD_ADAM) wide_s2[row[u]] = wv[u];
+        if (opt_has_slot2(OPT)) wide_s2[row[u]] = wv[u];
       }
     }
   }
@@ -517,12 +498,12 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
       raw[u] = *reinterpret_cast<const uint2*>(mv.payload + e[u] * kEmbDim + lane * 4);
       w[u] = *reinterpret_cast<float4*>(master + o[u]);
       if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
-      if (OPT == WD_ADAM) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
+      if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
       if (lane == 0) {
         dlv[u] = mv.dl[e[u]];
         ww[u] = wide[row[u]];
         if (OPT != WD_SGD) wa[u] = wide_s1[row[u]];
-        if (OPT == WD_ADAM) wv[u] = wide_s2[row[u]];
+        if (opt_has_slot2(OPT)) wv[u] = wide_s2[row[u]];
       }
     }
 #pragma unroll
@@ -556,7 +537,7 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
       opt_update<OPT>(w[u].w, g.w, a[u].w, v[u].w, oc);
       *reinterpret_cast<float4*>(master + o[u]) = w[u];
       if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o[u]) = a[u];
-      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
+      if (opt_has_slot2(OPT)) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
       uint2 pk;
       pk.x = pack_bf16x2(w[u].x, w[u].y);
       pk.y = pack_bf16x2(w[u].z, w[u].w);
@@ -565,7 +546,7 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
         opt_update<OPT>(ww[u], gw, wa[u], wv[u], oc);
         wide[row[u]] = ww[u];
         if (OPT != WD_SGD) wide_s1[row[u]] = wa[u];
-        if (OPT == WD_ADAM) wide_s2[row[u]] = wv[u];
+        if (opt_has_slot2(OPT)) wide_s2[row[u]] = wv[u];
         row_state[row[u]] = 0ull;   // ready for the next step
       }
     }
@@ -616,7 +597,7 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
       }
       w[u] = *reinterpret_cast<float4*>(master + (i - lo));
       if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + (i - lo));
-      if (OPT == WD_ADAM) v[u] = *reinterpret_cast<float4*>(s2 + (i - lo));
+      if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + (i - lo));
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -646,7 +627,7 @@ wd_dense_apply_kernel(PeerTable pt, SlabLayout sl, long long lo, long long hi, i
       }
       *reinterpret_cast<float4*>(master + (i - lo)) = w[u];
       if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + (i - lo)) = a[u];
-      if (OPT == WD_ADAM) *reinterpret_cast<float4*>(s2 + (i - lo)) = v[u];
+      if (opt_has_slot2(OPT)) *reinterpret_cast<float4*>(s2 + (i - lo)) = v[u];
       uint2 pk;
       pk.x = pack_bf16x2(w[u].x, w[u].y);
       pk.y = pack_bf16x2(w[u].z, w[u].w);

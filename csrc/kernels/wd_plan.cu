@@ -184,8 +184,13 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
     set_error("wd plan: unsupported shape (h1,h2 multiples of 64; h3 multiple of 256 <= 1024; dense_pad multiple of 64)");
     return nullptr;
   }
-  if (cfg->optimizer != WD_SGD && cfg->optimizer != WD_ADAGRAD && cfg->optimizer != WD_ADAM) {
-    set_error("wd plan: optimizer %d not available on the GPU path (sgd=0, adagrad=2, adam=3)", cfg->optimizer);
+  if (cfg->optimizer < WD_SGD || cfg->optimizer > WD_RMSPROP) {
+    set_error("wd plan: unknown optimizer id %d (sgd=0, adadelta=1, adagrad=2, adam=3, ftrl=4, rmsprop=5)", cfg->optimizer);
+    return nullptr;
+  }
+  if (cfg->dense_pad != 64) {
+    // the gather warps of the fused pull move the dense block as one 64-column chunk per row
+    set_error("wd plan: dense_pad must be 64 (got %d)", cfg->dense_pad);
     return nullptr;
   }
   auto* p = new dtf_wd_plan();
@@ -267,7 +272,7 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   p->in_slab<void>("signal", sl.signal, kMaxWorld * 64);   // barrier pads (diagnostics: bench/stress_overlap.py)
 
   const size_t ne = static_cast<size_t>(sh.rows_local) * kEmbDim;
-  const bool has1 = cfg->optimizer != WD_SGD, has2 = cfg->optimizer == WD_ADAM;
+  const bool has1 = opt_has_slot1(cfg->optimizer), has2 = opt_has_slot2(cfg->optimizer);
   bool ok = true;
   ok &= (p->emb_master = p->alloc<float>("emb_master", ne)) != nullptr;
   if (has1) ok &= (p->emb_s1 = p->alloc<float>("emb_slot1", ne)) != nullptr;
@@ -437,7 +442,7 @@ int dtf_wd_attach_ptrs(dtf_wd_plan* p, void* const* slabs) {
 
 int dtf_wd_init_params(dtf_wd_plan* p, unsigned long long seed, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
-  const float slot1_init = p->cfg.optimizer == WD_ADAGRAD ? 0.1f : 0.f;
+  const float slot1_init = opt_slot1_init(p->cfg.optimizer);
   wd_init_embedding_kernel<<<num_sms() * 8, 256, 0, st>>>(
       p->emb_master, reinterpret_cast<__nv_bfloat16*>(p->slab + p->sl.emb_bf16), p->emb_s1, p->emb_s2,
       reinterpret_cast<float*>(p->slab + p->sl.wide), p->wide_s1, p->wide_s2, p->sh.rows_local, p->cfg.world,
@@ -702,7 +707,10 @@ static int apply_dispatch(dtf_wd_plan* p, cudaStream_t st, int which) {
   switch (p->cfg.optimizer) {
     case WD_SGD: return apply_t<WD_SGD>(p, st, which);
     case WD_ADAGRAD: return apply_t<WD_ADAGRAD>(p, st, which);
-    default: return apply_t<WD_ADAM>(p, st, which);
+    case WD_ADAM: return apply_t<WD_ADAM>(p, st, which);
+    case WD_ADADELTA: return apply_t<WD_ADADELTA>(p, st, which);
+    case WD_FTRL: return apply_t<WD_FTRL>(p, st, which);
+    default: return apply_t<WD_RMSPROP>(p, st, which);
   }
 }
 

@@ -29,7 +29,7 @@ import torch
 
 from ..ops import _lib
 
-OPT_IDS = {"sgd": 0, "adagrad": 2, "adam": 3}
+OPT_IDS = {"sgd": 0, "adadelta": 1, "adagrad": 2, "adam": 3, "ftrl": 4, "rmsprop": 5}   # same ids as dtf_native.h
 
 
 @dataclass
@@ -359,7 +359,9 @@ class WideDeepTrainer:
         return self.buffer("prob", torch.float32)[:n]
 
     # ------------------------------------------------------------------ parameter-server shard state
-    _SLOT_NAMES = {"adagrad": ("Adagrad",), "adam": ("Adam", "Adam_1"), "sgd": ()}
+    # TF slot names per optimizer, in the order slot1, slot2 of the plan
+    _SLOT_NAMES = {"adagrad": ("Adagrad",), "adam": ("Adam", "Adam_1"), "sgd": (), "adadelta": ("Adadelta", "Adadelta_1"),
+                   "ftrl": ("Ftrl", "Ftrl_1"), "rmsprop": ("RMSProp", "RMSProp_1")}
 
     def named_shards(self) -> Dict[str, torch.Tensor]:
         self.join()
@@ -456,7 +458,7 @@ class TorchReference:
         self.cfg = cfg
         self.emb, self.wide = emb.clone().float(), wide.clone().float()
         self.p = {k: v.clone().float() for k, v in dense.items()}
-        init = 0.1 if cfg.optimizer == "adagrad" else 0.0
+        init = {"adagrad": 0.1, "ftrl": 0.1, "rmsprop": 1.0}.get(cfg.optimizer, 0.0)
         self.s1 = {k: torch.full_like(v, init) for k, v in self._all().items()}
         self.s2 = {k: torch.zeros_like(v) for k, v in self._all().items()}
         self.t = 0
@@ -516,11 +518,28 @@ class TorchReference:
         elif c.optimizer == "adagrad":
             s1_ = s1_ + g * g
             w_ = w_ - c.lr * g / s1_.sqrt()
-        else:
+        elif c.optimizer == "adam":
             lr_t = c.lr * (1 - 0.999 ** self.t) ** 0.5 / (1 - 0.9 ** self.t)
             s1_ = 0.9 * s1_ + 0.1 * g
             s2_ = 0.999 * s2_ + 0.001 * g * g
             w_ = w_ - lr_t * s1_ / (s2_.sqrt() + 1e-8)
+        elif c.optimizer == "adadelta":
+            s1_ = 0.95 * s1_ + 0.05 * g * g
+            u = (s2_ + 1e-8).sqrt() / (s1_ + 1e-8).sqrt() * g
+            s2_ = 0.95 * s2_ + 0.05 * u * u
+            w_ = w_ - c.lr * u
+        elif c.optimizer == "ftrl":
+            n_new = s1_ + g * g
+            sigma = (n_new.sqrt() - s1_.sqrt()) / c.lr
+            s2_ = s2_ + g - sigma * w_
+            w_ = -s2_ * c.lr / n_new.sqrt()
+            s1_ = n_new
+        elif c.optimizer == "rmsprop":
+            s1_ = s1_ + (g * g - s1_) * 0.1
+            s2_ = c.lr * g / (s1_ + 1e-10).sqrt()
+            w_ = w_ - s2_
+        else:
+            raise KeyError(c.optimizer)
         if rows is not None:
             w[rows], s1[rows], s2[rows] = w_, s1_, s2_
         else:

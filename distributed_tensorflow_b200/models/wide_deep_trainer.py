@@ -201,7 +201,8 @@ def run_wide_deep(flags) -> None:
         raise SystemExit("--model=wide_deep needs --device=cuda and a visible GPU")
     start = datetime.datetime.now()
     d = _Dist()
-    opt = flags.optimizer if flags.optimizer in ("sgd", "adagrad", "adam") else None
+    from .wide_deep import OPT_IDS
+    opt = flags.optimizer if flags.optimizer in OPT_IDS else None
     print("Use the optimizer: {}".format(flags.optimizer))
     if opt is None:
         print("Unknow optimizer: {}, exit now".format(flags.optimizer))

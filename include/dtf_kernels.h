@@ -101,7 +101,9 @@ int dtf_push_gemm_bf16(const void* dY, long long lddy, const void* W, long long 
  * device share that array, which keeps the previous call's contents (the used part is cleared at the
  * start of each call): calls whose GPU work overlaps race -- keep them stream-ordered.  The first
  * call on each device resolves the array's device address; issue it at start-up, before any stream
- * capture.  This entry point has no counterpart in the reference. */
+ * capture.  That address is cached per device for the life of the process: after a cudaDeviceReset
+ * it is stale, so a process that resets a device must not call this entry point on it again.
+ * This entry point has no counterpart in the reference. */
 int dtf_pull_gemm_noalloc_max_rows(void);
 int dtf_pull_gemm_bf16_noalloc(const unsigned long long* row_src, const void* dense_x, int slots,
                                int dense_cols, void* a_buf, const void* W, long long ldw, const float* bias,
@@ -151,10 +153,10 @@ typedef struct dtf_wd_config {
   int slots;          /* sparse ids per example (F) */
   int emb_dim;        /* must be 128 */
   int dense_in;       /* dense features per example */
-  int dense_pad;      /* dense block width inside the GEMM-1 operand (multiple of 64) */
+  int dense_pad;      /* dense block width inside the GEMM-1 operand: 64 */
   int h1, h2, h3;     /* hidden sizes; h3 multiple of 256 */
   long long emb_rows; /* global rows of the embedding (and wide) table */
-  int optimizer;      /* 0 sgd, 2 adagrad, 3 adam (same ids as dtf_native.h) */
+  int optimizer;      /* 0 sgd, 1 adadelta, 2 adagrad, 3 adam, 4 ftrl, 5 rmsprop (same ids as dtf_native.h) */
   int sync;           /* 1: sync-replica (sum all replicas, apply once); 0: async / Hogwild */
   int no_device_barrier; /* 1: caller orders ranks itself (several ranks emulated on one GPU) */
   float lr;
@@ -214,6 +216,14 @@ void dtf_wd_overlap_reset(dtf_wd_plan*);
 void dtf_wd_profile_enable(dtf_wd_plan*, int on);
 int dtf_wd_profile_read(dtf_wd_plan*, char* buf, size_t cap);
 int dtf_wd_profile_read_abs(dtf_wd_plan*, char* buf, size_t cap);  /* offsets from the first mark */
+
+/* The per-element optimizer rule of the ps-side apply kernels (reference trainer/task.py:41-56: sgd,
+ * adadelta, adagrad, adam, ftrl, rmsprop with TF-1 defaults), run on the host over n elements: lets
+ * CPU tests compare the device math with the NumPy optimizers.  `step` (>= 1) only matters for adam. */
+int dtf_opt_update_host(int optimizer, float* w, const float* g, float* slot1, float* slot2, long long n,
+                        float lr, long long step);
+float dtf_opt_slot1_init(int optimizer);
+int dtf_opt_num_slots(int optimizer);
 
 #ifdef __cplusplus
 }

@@ -125,3 +125,39 @@ def test_toy_model_loss_and_grads_closed_form():
     out = m.predict({"weight": np.float32(2), "bias": np.float32(10)}, {"keys": [[11.0], [2.0]], "features": [[1], [2]]})
     assert out["keys"].dtype == np.int32 and out["keys"].tolist() == [[11], [2]]
     assert out["prediction"].tolist() == [[12.0], [14.0]]
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_device_apply_rule_matches_numpy_optimizer(name):
+    """The per-element rule the CUDA ps-side apply kernels use (csrc/kernels/wd_optim.cuh, compiled for the
+    host into libdtf_kernels.so) against the NumPy optimizer of the same name: weights and both slots, five
+    steps, vectors with repeated sign changes.  Covers `--model=wide_deep --optimizer=<any of the six>`
+    (reference trainer/task.py:41-56) without needing a GPU."""
+    from distributed_tensorflow_b200.ops import _lib
+    L = _lib.lib()
+    L.dtf_opt_update_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_float,
+                                      C.c_longlong]
+    L.dtf_opt_slot1_init.restype = C.c_float
+    rng = np.random.RandomState(1)
+    n, lr = 257, 0.05
+    opt = get_optimizer(name, lr)
+    oid = OPTIMIZER_IDS[name]
+    store = {"w": (rng.randn(n) * 0.3).astype(np.float32)}
+    opt.ensure_slots(store, "w")
+    specs = opt.slot_specs("w")
+    slot_names = list(specs)
+    assert L.dtf_opt_num_slots(oid) == len(slot_names)
+    if slot_names:
+        assert abs(L.dtf_opt_slot1_init(oid) - specs[slot_names[0]]) < 1e-7
+    w = store["w"].copy()
+    s = [np.full(n, specs[k], np.float32) for k in slot_names]
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)
+    for t in range(1, 6):
+        g = (rng.randn(n) * (1.0 if t % 2 else 0.01)).astype(np.float32)
+        opt.apply(store, {"w": g})
+        rc = L.dtf_opt_update_host(oid, ptr(w), ptr(g), ptr(s[0]) if len(s) > 0 else None, ptr(s[1]) if len(s) > 1 else None,
+                                   n, lr, t)
+        assert rc == 0
+        assert np.allclose(w, store["w"], rtol=1e-4, atol=1e-5), (name, t, np.abs(w - store["w"]).max())
+        for k, arr in zip(slot_names, s):
+            assert np.allclose(arr, store[k], rtol=1e-4, atol=1e-7), (name, k, t)

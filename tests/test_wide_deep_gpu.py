@@ -256,3 +256,51 @@ def test_graphed_train_loop_trains_from_pinned_host_batches(sync):
     assert t.global_step() == step0 + 12 * G
     assert loop.h2d_bytes_per_step == cfg.batch * (cfg.slots * 4 + cfg.dense_in * 4 + 4)
     t.close()
+
+
+@pytest.mark.parametrize("opt", ["adadelta", "ftrl", "rmsprop"])
+def test_remaining_reference_optimizers_apply_the_host_checked_rule(opt):
+    """`--optimizer` accepts six names in the reference (trainer/task.py:41-56).  The three that the first
+    round left out run the same per-element rule as tests/test_optimizers.py checks on the host
+    (csrc/kernels/wd_optim.cuh): one ps-side apply on the GPU must reproduce that rule on the dense shard
+    (master weights and both slots), move the touched embedding rows only, and keep training finite."""
+    import ctypes as C
+    from distributed_tensorflow_b200.models.wide_deep import OPT_IDS
+    from distributed_tensorflow_b200.ops import _lib
+    cfg = _cfg(optimizer=opt, lr=0.05)
+    ts = _make(cfg, 1)
+    t = ts[0]
+    b = _batch(cfg, 3, t.device)
+    names = t._SLOT_NAMES[opt]
+    assert len(names) == 2 and all(("dense_flat/part_0/" + n) in t.named_shards() for n in names)
+    w0 = t.buffer("dense_master", torch.float32).clone()
+    s1_0 = t.buffer("dense_slot1", torch.float32).clone()
+    s2_0 = t.buffer("dense_slot2", torch.float32).clone()
+    emb0 = t.buffer("emb_master", torch.float32).clone()
+    t.step_compute(*b)
+    t.barrier(True)
+    torch.cuda.synchronize()
+    n = w0.numel()
+    g = t.buffer("dense_grad", torch.float32)[t.info.dense_lo: t.info.dense_hi].clone()
+    t.step_apply()
+    torch.cuda.synchronize()
+    L = _lib.lib()
+    L.dtf_opt_update_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_float,
+                                      C.c_longlong]
+    hw, hg, h1, h2 = (x.cpu().numpy().copy() for x in (w0, g, s1_0, s2_0))
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    assert L.dtf_opt_update_host(OPT_IDS[opt], p(hw), p(hg), p(h1), p(h2), n, cfg.lr, 1) == 0
+    _close(t.buffer("dense_master", torch.float32), torch.from_numpy(hw).to(t.device), 1e-4, 1e-6, "dense weights")
+    _close(t.buffer("dense_slot1", torch.float32), torch.from_numpy(h1).to(t.device), 1e-4, 1e-7, "dense slot 1")
+    _close(t.buffer("dense_slot2", torch.float32), torch.from_numpy(h2).to(t.device), 1e-4, 1e-7, "dense slot 2")
+    emb1 = t.buffer("emb_master", torch.float32)
+    nrow = t.info.rows_local
+    moved = (emb1[: nrow * cfg.emb_dim].view(nrow, -1) != emb0[: nrow * cfg.emb_dim].view(nrow, -1)).any(1)
+    touched = torch.zeros(nrow, dtype=torch.bool, device=t.device)
+    touched[b[0].long().reshape(-1)] = True
+    assert moved.any() and not (moved & ~touched).any()                        # only rows of this batch's ids move
+    for s in range(4, 10):                                                      # keeps training without blowing up
+        _run_sync_steps(ts, [[_batch(cfg, s, t.device)]])
+    assert np.isfinite(float(t.last_loss_sum())) and torch.isfinite(t.buffer("dense_master", torch.float32)).all()
+    assert t.global_step() == 7
+    t.close()
