@@ -328,6 +328,23 @@ class WideDeepTrainer:
         else:
             _lib.check(self._L.dtf_wd_step(self._h, a, b, c, self._stream()), "dtf_wd_step")
 
+    def set_barrier_timeout_ms(self, ms: int) -> None:
+        """How long a device barrier waits for a peer before it records an error (0 = forever)."""
+        self._L.dtf_wd_set_barrier_timeout_ms.restype = None
+        self._L.dtf_wd_set_barrier_timeout_ms.argtypes = [C.c_longlong]
+        self._L.dtf_wd_set_barrier_timeout_ms(int(ms))
+
+    def check_error(self) -> None:
+        """Raise ``ConnectionError`` if a device barrier of this plan gave up on a peer (dead or stalled
+        rank).  Cheap: one 4-byte read on a private stream, the training streams are not synchronised."""
+        self._L.dtf_wd_check_error.argtypes = [C.c_void_p]
+        rc = int(self._L.dtf_wd_check_error(self._h))
+        if rc > 0:
+            raise ConnectionError("rank %d: device barrier timed out waiting for rank %d (peer dead or stalled)"
+                                  % (self.rank, rc - 1))
+        if rc < 0:
+            raise RuntimeError("dtf_wd_check_error: " + _lib.lib().dtf_last_error().decode())
+
     def join(self) -> None:
         """Make the current stream wait for every ps-side apply issued so far (call before reading
         shards, predicting, checkpointing, or ending a CUDA-graph capture of overlapped steps)."""

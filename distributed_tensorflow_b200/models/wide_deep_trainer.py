@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import datetime
 import os
+import threading
 import time
 from typing import Dict, Optional
 
@@ -24,19 +25,66 @@ from .wide_deep import WideDeepConfig, WideDeepTrainer
 
 
 class _Dist:
-    """Thin wrapper so that single-process runs need no process group."""
+    """Rank, world and the host control plane of this process.
 
-    def __init__(self):
-        self.world = int(os.environ.get("WORLD_SIZE", "1"))
-        self.rank = int(os.environ.get("RANK", "0"))
-        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    Two ways in, one interface out (``barrier`` / ``all_gather_object`` / ``broadcast_object`` and
+    ``pg`` with torch.distributed's call shapes):
+
+    * ``TF_CONFIG`` (the reference's way, /root/reference/trainer/task.py:110-127): cluster and role come
+      from the environment, ``master`` is rank 0 and the chief, ``worker`` i is rank 1 + i, every task
+      starts its own :class:`Server` on the address the cluster lists for it, and all host-side
+      coordination goes through the C++ transport (``parallel/control.py``); no torchrun, no gloo.
+    * ``torchrun`` (RANK / WORLD_SIZE set): gloo for the collectives; rank 0 additionally hosts a control
+      store so that the checkpoint service below works the same way.
+    """
+
+    def __init__(self, timeout_ms: int = 30000, connect_retry_secs: float = 60.0):
+        from ..cluster import ClusterSpec, Server, parse_tf_config
+        from ..parallel.control import TransportGroup, rank_layout
         self.pg = None
-        if self.world > 1:
-            import torch.distributed as dist
-            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-            if not dist.is_initialized():
-                dist.init_process_group("gloo", rank=self.rank, world_size=self.world)
-            self.pg = dist
+        self.server = None
+        self.cluster = None
+        self.task_type, self.task_index = "master", 0
+        self.timeout_ms = int(timeout_ms)
+        tf_cfg = parse_tf_config() if "RANK" not in os.environ else None
+        if tf_cfg is not None:
+            self.cluster, self.task_type, self.task_index = tf_cfg.cluster, tf_cfg.task_type, tf_cfg.task_index
+            rank, self.world, self.store_addr = rank_layout(tf_cfg.cluster, tf_cfg.task_type, tf_cfg.task_index)
+            if rank is None:
+                raise ValueError("task type %r does not train (only master / worker do)" % tf_cfg.task_type)
+            self.rank = rank
+            self.server = Server(tf_cfg.cluster, job_name=tf_cfg.task_type, task_index=tf_cfg.task_index)
+            ndev = max(1, torch.cuda.device_count())
+            self.local_rank = self.rank % ndev       # CUDA_VISIBLE_DEVICES per task (one device each) also works
+            self.pg = TransportGroup(self.store_addr, self.rank, self.world, timeout_s=max(1.0, timeout_ms / 1000.0),
+                                     connect_retry_secs=connect_retry_secs)
+        else:
+            self.world = int(os.environ.get("WORLD_SIZE", "1"))
+            self.rank = int(os.environ.get("RANK", "0"))
+            self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+            if self.world > 1:
+                import torch.distributed as dist
+                os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+                if not dist.is_initialized():
+                    dist.init_process_group("gloo", rank=self.rank, world_size=self.world)
+                self.pg = dist
+            if self.rank == 0:
+                self.server = Server(ClusterSpec({"master": ["127.0.0.1:0"]}), "master", 0)
+            self.store_addr = self.broadcast_object("127.0.0.1:%d" % self.server.port if self.rank == 0 else None)
+        # names on the control store are scoped by a per-incarnation nonce chosen by the chief
+        self.nonce = self.broadcast_object("%x" % int(time.time() * 1000) if self.rank == 0 else None)
+
+    @property
+    def is_chief(self) -> bool:
+        return self.rank == 0
+
+    def control_client(self):
+        """A fresh connection to the control store (one per thread that blocks on queues)."""
+        from ..session import PSClient
+        return PSClient(self.store_addr, timeout_ms=self.timeout_ms, connect_retry_secs=10.0)
+
+    def name(self, what: str) -> str:
+        return "wd/%s/%s" % (self.nonce, what)
 
     def barrier(self):
         if self.pg:
@@ -56,6 +104,13 @@ class _Dist:
         self.pg.broadcast_object_list(box, src=src)
         return box[0]
 
+    def close(self) -> None:
+        if self.pg is not None and hasattr(self.pg, "close"):
+            self.pg.close()
+        if self.server is not None:
+            self.server.stop()
+            self.server = None
+
 
 def make_trainer(cfg: WideDeepConfig, d: _Dist) -> WideDeepTrainer:
     torch.cuda.set_device(d.local_rank)
@@ -66,21 +121,48 @@ def make_trainer(cfg: WideDeepConfig, d: _Dist) -> WideDeepTrainer:
 
 
 class WideDeepCheckpointer:
-    """Collective save / restore of the sharded model in TF checkpoint-V2 layout."""
+    """Save / restore of the sharded model in TF checkpoint-V2 layout: every rank writes
+    the bundle shard of its own ps shard, the chief merges the indices.
+
+    Two ways to save.  :meth:`save` is the plain collective (every rank calls it at the same step).
+    The *service* is what the Supervisor's timer thread uses (reference trainer/task.py:215-223,
+    ``save_model_secs=60``): :meth:`start_service` starts one thread per non-chief rank that waits on a
+    queue of the control store; the chief's :meth:`request_save` posts one request per rank, writes its
+    own shard, collects the acknowledgements and merges.  Shards are copied device -> pinned host on a
+    side stream without synchronising the training streams, so a checkpoint taken during Hogwild
+    training is not an atomic cut -- exactly like TF's (the ps snapshots while workers keep applying).
+    """
 
     def __init__(self, trainer: WideDeepTrainer, d: _Dist, logdir: str, max_to_keep: int = 5):
         self.tr, self.d, self.logdir = trainer, d, logdir
         self._saver = Saver(max_to_keep=max_to_keep)      # bookkeeping of retained checkpoints (chief)
-        self._side = torch.cuda.Stream(device=trainer.device)
+        self._cuda = getattr(trainer, "device", torch.device("cpu")).type == "cuda"
+        self._side = torch.cuda.Stream(device=trainer.device) if self._cuda else None
         self._pinned: Dict[str, torch.Tensor] = {}
+        self._lock = threading.Lock()                       # one snapshot at a time per rank
+        self._svc: Optional[threading.Thread] = None
+        self._svc_stop = threading.Event()
+        self._svc_error: Optional[BaseException] = None
+        self._ctl = None
         if d.rank == 0:
             os.makedirs(logdir, exist_ok=True)
             self._saver.recover_last_checkpoints(logdir)
 
-    def _snapshot_to_host(self) -> Dict[str, np.ndarray]:
-        shards = self.tr.named_shards()
-        self._side.wait_stream(torch.cuda.current_stream(self.tr.device))
-        with torch.cuda.stream(self._side):
+    @property
+    def last_checkpoints(self):
+        return list(self._saver._last_checkpoints)
+
+    def _snapshot_to_host(self, wait_for_training: bool = True) -> Dict[str, np.ndarray]:
+        """Host views of this rank's shard (pinned staging buffers, reused: callers hold ``_lock`` until
+        they are done with the arrays)."""
+        if not self._cuda:
+            return {k: t.detach().clone().numpy() for k, t in self.tr.named_shards().items()}
+        if wait_for_training:
+            shards = self.tr.named_shards()                 # current stream waits for the pending applies
+            self._side.wait_stream(torch.cuda.current_stream(self.tr.device))
+        else:
+            shards = self.tr._named_shards()                # service thread: no dependency on the training streams
+        with torch.cuda.device(self.tr.device), torch.cuda.stream(self._side):
             for k, t in shards.items():
                 if k not in self._pinned:
                     self._pinned[k] = torch.empty(t.shape, dtype=t.dtype).pin_memory()
@@ -88,37 +170,110 @@ class WideDeepCheckpointer:
         self._side.synchronize()
         return {k: v.numpy() for k, v in self._pinned.items()}
 
+    def _part(self, prefix: str, rank: int) -> str:
+        return "%s_temp/part-%05d" % (prefix, rank)
+
+    def _write_part(self, prefix: str, step: int, wait_for_training: bool) -> None:
+        with self._lock:                                    # one snapshot + write at a time per rank
+            host = self._snapshot_to_host(wait_for_training)
+            if self.d.rank == 0:
+                host["global_step"] = np.array(step, dtype=np.int64)
+            os.makedirs(os.path.dirname(self._part(prefix, self.d.rank)), exist_ok=True)
+            _bundle.write_bundle(self._part(prefix, self.d.rank), host)
+
+    def _merge(self, prefix: str) -> None:
+        _bundle.merge_bundles([self._part(prefix, r) for r in range(self.d.world)], prefix)
+        try:
+            os.rmdir(prefix + "_temp")
+        except OSError:
+            pass
+        s = self._saver
+        s._last_checkpoints.append(prefix)
+        while len(s._last_checkpoints) > s.max_to_keep:
+            s._delete(s._last_checkpoints.pop(0))
+        update_checkpoint_state(self.logdir, prefix, s._last_checkpoints)
+
     def save(self, step: int) -> str:
-        """Every rank must call this at the same step."""
+        """Collective: every rank must call this at the same step."""
         prefix = os.path.join(self.logdir, "model.ckpt-%d" % step)
-        part = "%s_temp/part-%05d" % (prefix, self.d.rank)
         if self.d.rank == 0:
-            os.makedirs(os.path.dirname(part), exist_ok=True)
+            os.makedirs(prefix + "_temp", exist_ok=True)
         self.d.barrier()
-        host = self._snapshot_to_host()
-        if self.d.rank == 0:
-            host["global_step"] = np.array(step, dtype=np.int64)
-        _bundle.write_bundle(part, host)
+        self._write_part(prefix, step, wait_for_training=True)
         self.d.barrier()
         if self.d.rank == 0:
-            _bundle.merge_bundles(["%s_temp/part-%05d" % (prefix, r) for r in range(self.d.world)], prefix)
-            try:
-                os.rmdir(prefix + "_temp")
-            except OSError:
-                pass
-            s = self._saver
-            s._last_checkpoints.append(prefix)
-            while len(s._last_checkpoints) > s.max_to_keep:
-                s._delete(s._last_checkpoints.pop(0))
-            update_checkpoint_state(self.logdir, prefix, s._last_checkpoints)
+            self._merge(prefix)
         self.d.barrier()
         return prefix
 
-    def restore_latest(self) -> Optional[int]:
-        """Chief semantics of Supervisor.prepare_session: restore if a checkpoint exists, else None."""
-        path = self.d.broadcast_object(latest_checkpoint(self.logdir) if self.d.rank == 0 else None)
-        if path is None:
-            return None
+    # ------------------------------------------------------------------ checkpoint service
+    def _req_queue(self, rank: int) -> str:
+        return self.d.name("ckpt_req/%d" % rank)
+
+    def start_service(self) -> None:
+        """Non-chief ranks: serve the chief's save requests from a background thread until
+        :meth:`stop_service`.  (The chief needs no thread; its Supervisor timer calls request_save.)"""
+        if self.d.rank == 0 or self._svc is not None:
+            return
+        self._ctl = self.d.control_client()
+        self._svc_stop.clear()
+
+        def loop():
+            try:
+                while not self._svc_stop.is_set():
+                    step = self._ctl.dequeue(self._req_queue(self.d.rank), timeout_ms=200)
+                    if step is None:
+                        continue
+                    prefix = os.path.join(self.logdir, "model.ckpt-%d" % step)
+                    self._write_part(prefix, step, wait_for_training=False)
+                    self._ctl.enqueue(self.d.name("ckpt_done"), self.d.rank)
+            except BaseException as e:  # noqa: BLE001  (surfaced by stop_service)
+                self._svc_error = e
+
+        self._svc = threading.Thread(target=loop, name="wd-checkpoint-service", daemon=True)
+        self._svc.start()
+
+    def stop_service(self) -> None:
+        if self._svc is not None:
+            self._svc_stop.set()
+            self._svc.join(30)
+            self._svc = None
+        if self._ctl is not None:
+            self._ctl.close()
+            self._ctl = None
+        if self._svc_error is not None:
+            e, self._svc_error = self._svc_error, None
+            raise e
+
+    def request_save(self, step: int, timeout_s: float = 600.0, abort=None) -> Optional[str]:
+        """Chief only, any thread: checkpoint every rank's shard as of "about now" without stopping training.
+        ``abort()`` turning true (the Supervisor is stopping) gives the save up and returns None."""
+        assert self.d.rank == 0
+        prefix = os.path.join(self.logdir, "model.ckpt-%d" % step)
+        os.makedirs(prefix + "_temp", exist_ok=True)
+        ctl = self.d.control_client()
+        try:
+            for r in range(1, self.d.world):
+                ctl.enqueue(self._req_queue(r), int(step))
+            self._write_part(prefix, step, wait_for_training=False)
+            deadline = time.time() + timeout_s
+            seen = set()
+            while len(seen) < self.d.world - 1:
+                if abort is not None and abort():
+                    return None
+                if time.time() > deadline:
+                    raise ConnectionError("checkpoint %s: ranks %s did not write their shard within %.0f s"
+                                          % (prefix, sorted(set(range(1, self.d.world)) - seen), timeout_s))
+                r = ctl.dequeue(self.d.name("ckpt_done"), timeout_ms=500)
+                if r is not None:
+                    seen.add(int(r))
+        finally:
+            ctl.close()
+        self._merge(prefix)
+        return prefix
+
+    def restore_from(self, path: str) -> int:
+        """This rank's shard (and the step) out of a merged checkpoint."""
         with _bundle.BundleReader(path) as r:
             if r.num_shards != self.d.world:
                 raise RuntimeError("checkpoint %s was written by %d ranks, this job has %d" % (path, r.num_shards, self.d.world))
@@ -126,6 +281,14 @@ class WideDeepCheckpointer:
             tensors = {k: r.get_tensor(k) for k in names}
             step = int(r.get_tensor("global_step"))
         self.tr.load_shards(tensors, step=step)
+        return step
+
+    def restore_latest(self) -> Optional[int]:
+        """Collective.  Chief semantics of Supervisor.prepare_session: restore if a checkpoint exists, else None."""
+        path = self.d.broadcast_object(latest_checkpoint(self.logdir) if self.d.rank == 0 else None)
+        if path is None:
+            return None
+        step = self.restore_from(path)
         self.d.barrier()
         return step
 
@@ -196,12 +359,110 @@ def synthetic_batch(cfg: WideDeepConfig, gen: torch.Generator, device):
     return ids.to(device, non_blocking=True), dense.to(device, non_blocking=True), labels.to(device, non_blocking=True)
 
 
-def run_wide_deep(flags) -> None:
-    if flags.device != "cuda" or not torch.cuda.is_available():
+class WideDeepSession:
+    """What :class:`Supervisor` manages for the GPU job: readiness, init / restore, the step counter.
+
+    The chief decides "restore checkpoint X" or "initialise" (Supervisor.prepare_or_wait_for_session, the
+    restore-or-init of reference trainer/task.py:215-226) and publishes the decision on the control
+    store; every other rank polls ``is_ready()`` like a TF non-chief, and when the decision is there
+    loads its own shard of X (or initialises its shard) and joins the barrier that ends start-up.
+    """
+
+    def __init__(self, tr: WideDeepTrainer, d: _Dist, ckpt: WideDeepCheckpointer):
+        self.tr, self.d, self.ckpt = tr, d, ckpt
+        self.model = WideDeepServingSpec(tr.export_config())
+        self.steps = 0                     # steps of this rank; restored from the checkpoint
+        self._ready = False
+        self._ctl = d.control_client()
+
+    # -- chief ---------------------------------------------------------------------------------
+    def _publish(self, decision) -> None:
+        from ..parallel.control import put_object
+        put_object(self._ctl, self.d.name("start"), decision)
+
+    def _finish_startup(self) -> None:
+        if self.tr.device.type == "cuda":
+            torch.cuda.synchronize(self.tr.device)
+        self.d.barrier()                   # every shard is in place before anyone pulls from a peer
+        self._ready = True
+
+    def run_init(self) -> None:
+        self._publish({"restore": None})
+        self.tr.init_params()
+        self._finish_startup()
+
+    def restore(self, path: str) -> None:
+        self._publish({"restore": path})
+        self.steps = self.ckpt.restore_from(path) // max(1, self.d.world)
+
+    def end_restore(self) -> None:
+        self._finish_startup()
+
+    # -- every rank ------------------------------------------------------------------------------
+    def is_ready(self) -> bool:
+        if self._ready or self.d.rank == 0:
+            return self._ready
+        from ..parallel.control import get_object
+        decision = get_object(self._ctl, self.d.name("start"))
+        if decision is None:
+            return False
+        if decision["restore"] is None:
+            self.tr.init_params()
+        else:
+            self.steps = self.ckpt.restore_from(decision["restore"]) // max(1, self.d.world)
+        self._finish_startup()
+        return True
+
+    def global_step(self) -> int:
+        """Like the reference, every worker's step bumps the shared counter (task.py:138)."""
+        return self.steps * self.d.world
+
+    def snapshot(self) -> Dict[str, np.ndarray]:
+        """Shapes only (zero-stride views), for graph.pbtxt; checkpoints go through the checkpointer."""
+        return {k: np.broadcast_to(np.float32(0), tuple(t.shape)) for k, t in self.tr._named_shards().items()}
+
+    def close(self) -> None:
+        self._ctl.close()
+
+
+class WideDeepSaver:
+    """The ``saver`` the Supervisor's timer thread calls (``saver.save(sess, save_path, global_step)``):
+    triggers the checkpoint service, so periodic checkpoints never synchronise the training streams."""
+
+    def __init__(self, ckpt: WideDeepCheckpointer, timeout_s: float = 600.0):
+        self.ckpt, self.timeout_s = ckpt, timeout_s
+        self.abort = None                   # set to Supervisor.should_stop once the supervisor exists
+
+    @property
+    def last_checkpoints(self):
+        return self.ckpt.last_checkpoints
+
+    def recover_last_checkpoints(self, logdir: str) -> None:
+        pass                                # done by the checkpointer on the chief
+
+    def restore(self, sess: WideDeepSession, path: str):
+        sess.restore(path)
+        return [path]
+
+    def save(self, sess: WideDeepSession, save_path: str, global_step=None) -> str:
+        return self.ckpt.request_save(int(global_step if global_step is not None else sess.global_step()),
+                                      timeout_s=self.timeout_s, abort=self.abort)
+
+
+def run_wide_deep(flags, auto_stop: bool = False, trainer_factory=None) -> None:
+    """The reference's distributed main() (trainer/task.py:109-261) for the B200 wide-and-deep job:
+    roles from TF_CONFIG (or torchrun), one Server per task, Supervisor-managed session with the 60 s
+    checkpoint timer and chief duties, master-only export, optional ps auto-stop.
+
+    ``trainer_factory(cfg, d)`` replaces the GPU trainer in the CPU tests of this lifecycle
+    (tests/test_wide_deep_lifecycle.py); product runs always take the CUDA path."""
+    from ..supervisor import Supervisor
+    from .wide_deep import OPT_IDS
+    if trainer_factory is None and (flags.device != "cuda" or not torch.cuda.is_available()):
         raise SystemExit("--model=wide_deep needs --device=cuda and a visible GPU")
     start = datetime.datetime.now()
-    d = _Dist()
-    from .wide_deep import OPT_IDS
+    timeout_ms = int(getattr(flags, "ps_timeout_ms", 30000))
+    d = _Dist(timeout_ms=timeout_ms, connect_retry_secs=float(getattr(flags, "connect_retry_secs", 60)))
     opt = flags.optimizer if flags.optimizer in OPT_IDS else None
     print("Use the optimizer: {}".format(flags.optimizer))
     if opt is None:
@@ -209,51 +470,84 @@ def run_wide_deep(flags) -> None:
         raise SystemExit(1)
     cfg = WideDeepConfig(emb_rows=flags.embedding_rows, emb_dim=flags.embedding_dim, batch=flags.batch_size,
                          optimizer=opt, lr=flags.learning_rate, sync=bool(flags.sync_replicas))
-    tr = make_trainer(cfg, d)
-    is_chief = d.rank == 0
+    tr = (trainer_factory or make_trainer)(cfg, d)
+    on_gpu = tr.device.type == "cuda"
+    tr.set_barrier_timeout_ms(timeout_ms)
+    is_chief = d.is_chief
     logdir = getattr(flags, "checkpoint_path", None) or getattr(flags, "checkpoint_dir")
     out_dir = getattr(flags, "output_path", None) or getattr(flags, "tensorboard_dir")
     ckpt = WideDeepCheckpointer(tr, d, logdir)
-    restored = ckpt.restore_latest()
-    if restored is None:
-        tr.init_params()
-        torch.cuda.synchronize()
-        d.barrier()
-    step0 = restored or 0
-    print("Save tensorboard files into: {}".format(out_dir))
-    writer = FileWriter(out_dir, filename_suffix=".rank%d" % d.rank)
-    print("Run training with epoch number: {}".format(flags.max_epochs))
-    gen = torch.Generator().manual_seed(100 + d.rank + 7919 * step0)
-    steps_per_epoch = max(1, flags.train_steps // max(1, flags.max_epochs))
-    last_save = time.time()
-    ckpt.save(step0)                                       # Supervisor: first save right away
-    step = step0
-    torch.cuda.set_stream(torch.cuda.Stream(device=tr.device, priority=-1))   # compute outranks the ps-side apply
-    for epoch in range(flags.max_epochs):
-        for _ in range(steps_per_epoch):
-            batch = synthetic_batch(cfg, gen, torch.device("cpu"))
-            if d.world > 1:
-                # copy-engine transfers are kept away from the device-barrier kernels of the overlapped apply
-                # (they stalled intermittently when mixed inside CUDA graphs); the host-side
-                # batch generation above is far longer than the apply, so this wait is normally already over
-                tr.join()
-            tr.step(*(t.to(tr.device) for t in batch))
-            step += 1
-        if epoch % flags.checkpoint_period == 0:
-            loss = float(tr.last_loss_sum()) / cfg.batch
-            print("Epoch: {}, loss: {}".format(epoch, loss))
-            if is_chief:
-                writer.add_summary(Summary([("loss", loss)]), step * d.world)
-        want = d.broadcast_object(time.time() - last_save >= flags.save_model_secs)
-        if want:
-            torch.cuda.synchronize()
-            ckpt.save(step)
-            last_save = time.time()
-    writer.close()
-    torch.cuda.synchronize()
-    print("[{}] End of distributed training.".format(datetime.datetime.now() - start))
+    session = WideDeepSession(tr, d, ckpt)
+    saver = WideDeepSaver(ckpt, timeout_s=max(5.0, 4.0 * timeout_ms / 1000.0))
+    sv = Supervisor(is_chief=is_chief, logdir=logdir, summary_op=None, saver=saver,
+                    global_step="global_step", save_model_secs=float(getattr(flags, "save_model_secs", 60)),
+                    recovery_wait_secs=min(1.0, float(getattr(flags, "recovery_wait_secs", 30))),
+                    session_factory=lambda target: session)
+    saver.abort = sv.should_stop
+    failed = None
     try:
-        export_wide_deep(tr, d, flags.saved_model_path, flags.model_version)
-    except Exception as e:  # noqa: BLE001  (reference logs export failures and carries on)
+        ckpt.start_service()               # non-chief ranks answer the chief's checkpoint requests from now on
+        with sv.managed_session(d.server.target if d.server is not None else "") as sess:
+            print("Save tensorboard files into: {}".format(out_dir))
+            writer = FileWriter(out_dir, filename_suffix=".rank%d" % d.rank)
+            print("Run training with epoch number: {}".format(flags.max_epochs))
+            gen = torch.Generator().manual_seed(100 + d.rank + 7919 * sess.steps)
+            steps_per_epoch = max(1, flags.train_steps // max(1, flags.max_epochs))
+            if on_gpu:
+                torch.cuda.set_stream(torch.cuda.Stream(device=tr.device, priority=-1))   # compute outranks the ps-side apply
+            for epoch in range(flags.max_epochs):
+                for _ in range(steps_per_epoch):
+                    batch = synthetic_batch(cfg, gen, torch.device("cpu"))
+                    if d.world > 1:
+                        # copy-engine transfers are kept away from the device-barrier kernels of the overlapped apply
+                        # (they stalled intermittently when mixed inside CUDA graphs); the host-side
+                        # batch generation above is far longer than the apply, so this wait is normally already over
+                        tr.join()
+                    tr.step(*(t.to(tr.device) for t in batch))
+                    sess.steps += 1
+                tr.check_error()           # a peer that stopped answering the device barriers: ConnectionError
+                if sv.should_stop():
+                    break
+                if epoch % flags.checkpoint_period == 0:
+                    loss = float(tr.last_loss_sum()) / cfg.batch
+                    print("Epoch: {}, loss: {}".format(epoch, loss))
+                    if is_chief:
+                        writer.add_summary(Summary([("loss", loss)]), sess.global_step())
+            writer.close()
+            if on_gpu:
+                torch.cuda.synchronize()
+            tr.check_error()
+            print("[{}] End of distributed training.".format(datetime.datetime.now() - start))
+            d.barrier()                    # every rank is done stepping before the chief stops its services
+        d.barrier()                        # the chief's last timer checkpoint (if any) has been served
+        ckpt.stop_service()
+        try:
+            export_wide_deep(tr, d, flags.saved_model_path, flags.model_version)
+        except ConnectionError:
+            raise
+        except Exception as e:  # noqa: BLE001  (reference logs export failures and carries on)
+            print(e)
+        if auto_stop and d.cluster is not None and "ps" in d.cluster.jobs:
+            # auto_stop_ps/task.py:270-272: one token per training task on every ps task's queue
+            from ..session import PSClient
+            from ..trainer_lib import done_queue_name
+            for i in range(d.cluster.num_tasks("ps")):
+                c = PSClient(d.cluster.task_address("ps", i), timeout_ms=timeout_ms, connect_retry_secs=10.0)
+                c.enqueue(done_queue_name(i), 1)
+                c.close()
+    except ConnectionError as e:
+        # a lost peer is fatal for the GPU job (its shard of every variable is gone): report and exit non-zero
         print(e)
-    tr.close()
+        failed = e
+    except Exception as e:  # noqa: BLE001  (reference task.py:260-261 swallows everything else)
+        print(e)
+    finally:
+        try:
+            ckpt.stop_service()
+        except Exception as e:  # noqa: BLE001
+            print(e)
+        if failed is None:
+            tr.close()
+        d.close()
+    if failed is not None:
+        os._exit(1)                        # peers' mappings may be gone; skip CUDA teardown that could block

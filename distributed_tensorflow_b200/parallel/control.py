@@ -48,6 +48,23 @@ def rank_layout(cluster: ClusterSpec, task_type: str, task_index: int) -> Tuple[
     return rank, world, store
 
 
+def put_object(client: PSClient, name: str, obj) -> None:
+    """Store a picklable object as a named variable of the control store."""
+    blob = pickle.dumps(obj, protocol=4)
+    pad = (-len(blob)) % 4
+    arr = np.frombuffer(blob + b"\0" * pad, dtype=np.int32)
+    client.init_var(name, np.concatenate([np.array([len(blob)], np.int32), arr]), overwrite=True)
+
+
+def get_object(client: PSClient, name: str, default=None):
+    """Inverse of :func:`put_object`; ``default`` when the variable does not exist (yet)."""
+    if client.var_info(name) is None:
+        return default
+    arr = client.pull(name)
+    n = int(arr[0])
+    return pickle.loads(arr[1:].tobytes()[:n])
+
+
 class TransportGroup:
     """Collectives of ``world`` ranks through one control store.  Every rank must make the same calls in
     the same order.  A peer that does not show up within ``timeout_s`` raises ``ConnectionError`` (a dead
@@ -65,15 +82,10 @@ class TransportGroup:
 
     # -- helpers -------------------------------------------------------------------------------
     def _put(self, name: str, obj) -> None:
-        blob = pickle.dumps(obj, protocol=4)
-        pad = (-len(blob)) % 4
-        arr = np.frombuffer(blob + b"\0" * pad, dtype=np.int32)
-        self._c.init_var(name, np.concatenate([np.array([len(blob)], np.int32), arr]), overwrite=True)
+        put_object(self._c, name, obj)
 
     def _get(self, name: str):
-        arr = self._c.pull(name)
-        n = int(arr[0])
-        return pickle.loads(arr[1:].tobytes()[:n])
+        return get_object(self._c, name)
 
     def _take(self, queue: str) -> None:
         deadline = time.time() + self.timeout_s

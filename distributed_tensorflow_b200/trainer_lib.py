@@ -68,8 +68,15 @@ def _flag(flags, name, default):
 def run(flags, legacy: bool = False, auto_stop: bool = False) -> None:
     variant = Variant(flags, legacy=legacy, auto_stop=auto_stop)
     if _flag(flags, "model", "linear") == "wide_deep":
+        # GPU job: master / worker tasks train (every rank is also a ps shard in HBM); a task started with
+        # the ps role hosts the control-plane store and leaves like any other ps (forever / auto-stop)
+        cfg = parse_tf_config()
+        if cfg is not None and cfg.task_type == "ps":
+            server = Server(cfg.cluster, job_name=cfg.task_type, task_index=cfg.task_index)
+            _run_ps_task(variant, cfg, server, int(_flag(flags, "ps_timeout_ms", 30000)))
+            return
         from .models.wide_deep_trainer import run_wide_deep
-        run_wide_deep(flags)
+        run_wide_deep(flags, auto_stop=auto_stop)
         return
 
     train_x, train_y = make_toy_data()
@@ -130,6 +137,26 @@ def _graph_bytes(model) -> bytes:
         return b""
 
 
+def _run_ps_task(variant, cfg, server, timeout_ms: int) -> None:
+    """The ps role: plain = ``server.join()`` forever (reference trainer/task.py:121-122); auto-stop = wait
+    for one token per worker and per master on this ps's queue, then exit (auto_stop_ps/task.py:137-150)."""
+    cluster, task_index = cfg.cluster, cfg.task_index
+    if not variant.auto_stop:
+        server.join()
+        return
+    worker_number = cluster.num_tasks("worker") if "worker" in cluster.jobs else 0
+    master_worker_number = worker_number + 1        # auto_stop_ps/task.py:117-121 assumes exactly one master
+    me = PSClient(cluster.task_address("ps", task_index), timeout_ms=timeout_ms)
+    me.queue_create(done_queue_name(task_index), master_worker_number)
+    for i in range(master_worker_number):
+        while me.dequeue(done_queue_name(task_index), timeout_ms=1000) is None:
+            pass
+        logging.info("{} workers are already done".format(i + 1))
+    logging.info("PS exists after all workers done")
+    me.close()
+    server.stop()
+
+
 def _run_distributed(variant, cfg, model, optimizer, train_x, train_y, t0) -> None:
     flags = variant.flags
     cluster, task_type, task_index = cfg.cluster, cfg.task_type, cfg.task_index
@@ -142,19 +169,7 @@ def _run_distributed(variant, cfg, model, optimizer, train_x, train_y, t0) -> No
     timeout_ms = int(_flag(flags, "ps_timeout_ms", 30000))
 
     if task_type == "ps":
-        if not variant.auto_stop:
-            server.join()
-            return
-        # auto-stop: wait for one token per worker and per master on this ps's queue, then exit
-        me = PSClient(cluster.task_address("ps", task_index), timeout_ms=timeout_ms)
-        me.queue_create(done_queue_name(task_index), master_worker_number)
-        for i in range(master_worker_number):
-            while me.dequeue(done_queue_name(task_index), timeout_ms=1000) is None:
-                pass
-            logging.info("{} workers are already done".format(i + 1))
-        logging.info("PS exists after all workers done")
-        me.close()
-        server.stop()
+        _run_ps_task(variant, cfg, server, timeout_ms)
         return
 
     if task_type not in ("worker", "master"):

@@ -130,3 +130,65 @@ def test_trainer_entry_point_two_ranks(tmp_path):
     from distributed_tensorflow_b200.checkpoint import BundleReader
     with BundleReader(str(tmp_path / "saved_model" / "1" / "variables" / "variables")) as r:
         assert {"embedding/part_0", "embedding/part_1", "dense_flat/part_0", "dense_flat/part_1"} <= set(r.keys())
+
+
+def _tf_config_procs(tmp_path, extra_args=(), extra_env=None, roles=("master", "worker")):
+    """Start the wide-and-deep job the reference's way: one process per task, only TF_CONFIG set (no torchrun)."""
+    import json
+    import socket
+    socks = [socket.socket() for _ in range(3)]
+    for s in socks:
+        s.bind(("127.0.0.1", 0))
+    ports = [s.getsockname()[1] for s in socks]
+    for s in socks:
+        s.close()
+    cluster = {"ps": ["127.0.0.1:%d" % ports[0]], "master": ["127.0.0.1:%d" % ports[1]], "worker": ["127.0.0.1:%d" % ports[2]]}
+    procs = {}
+    for role in ("ps",) + tuple(roles):
+        env = dict(os.environ)
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+            env.pop(k, None)
+        env["PYTHONPATH"] = REPO
+        env["TF_CONFIG"] = json.dumps({"cluster": cluster, "task": {"type": role, "index": 0}})
+        env.update((extra_env or {}).get(role, {}))
+        args = [sys.executable, "-m", "auto_stop_ps.task", "--model=wide_deep", "--device=cuda", "--embedding_rows=50000",
+                "--batch_size=512", "--train_steps=30", "--max_epochs=3", "--learning_rate=0.05", "--ps_timeout_ms=10000",
+                *extra_args]
+        procs[role] = subprocess.Popen(args, cwd=str(tmp_path), env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    return procs
+
+
+def test_two_gpu_job_started_from_tf_config_only(tmp_path):
+    """ps + master + worker processes with nothing but TF_CONFIG (reference trainer/task.py:110-127,
+    auto_stop_ps/task.py): rendezvous, slab-fd exchange and barriers over the C++ transport, Supervisor
+    checkpoints served by both ranks, master-only export, the ps leaves once both are done."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    procs = _tf_config_procs(tmp_path)
+    out = {k: p.communicate(timeout=300)[0] for k, p in procs.items()}
+    assert all(p.returncode == 0 for p in procs.values()), out
+    assert "End of distributed training." in out["master"] and "End of distributed training." in out["worker"]
+    files = os.listdir(tmp_path / "checkpoint")
+    assert "model.ckpt-0.data-00000-of-00002" in files and "model.ckpt-0.data-00001-of-00002" in files
+    assert (tmp_path / "checkpoint" / "graph.pbtxt").exists()
+    assert (tmp_path / "saved_model" / "1" / "saved_model.pb").exists()
+
+
+def test_survivor_exits_non_zero_when_its_peer_dies(tmp_path):
+    """Kill the worker mid-run: the master's device barriers give up after --ps_timeout_ms, the error flag
+    turns into ConnectionError and the process exits 1 instead of hanging."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import time
+    procs = _tf_config_procs(tmp_path, extra_args=("--train_steps=200000", "--max_epochs=2000", "--ps_timeout_ms=5000"))
+    deadline = time.time() + 120
+    while time.time() < deadline and not (tmp_path / "checkpoint" / "checkpoint").exists():
+        time.sleep(0.5)                                   # both ranks are up and training once the first checkpoint exists
+    time.sleep(2.0)
+    procs["worker"].kill()
+    t0 = time.time()
+    out = procs["master"].communicate(timeout=120)[0]
+    procs["ps"].kill()
+    assert procs["master"].returncode == 1, out
+    assert "timed out waiting for rank 1" in out or "missing or dead" in out or "did not write their shard" in out, out
+    assert time.time() - t0 < 90
