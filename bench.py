@@ -155,7 +155,10 @@ def main() -> int:
     for _ in range(args.pool):
         ids = torch.randint(0, cfg.emb_rows, (cfg.batch, cfg.slots), generator=g, dtype=torch.int32).pin_memory()
         dense = torch.randn(cfg.batch, cfg.dense_in, generator=g).pin_memory()
-        labels = (torch.rand(cfg.batch, generator=g) < 0.25).float().pin_memory()
+        # learnable target (same rule as models/wide_deep_trainer.synthetic_batch): depends on two dense
+        # features and on the parity of the first id, so the reported loss moves when training works
+        logit = dense[:, 0] - 0.5 * dense[:, 1] + (ids[:, 0] % 2).float() - 0.5
+        labels = (torch.rand(cfg.batch, generator=g) < torch.sigmoid(logit)).float().pin_memory()
         pool_h.append((ids, dense, labels))
     pool_d = [tuple(t.to(dev) for t in b) for b in pool_h]
     s_ids, s_dense, s_labels = (torch.empty_like(t, device=dev) for t in pool_h[0])   # static graph inputs
@@ -170,10 +173,13 @@ def main() -> int:
         s_dense.copy_(b[1], non_blocking=True)
         s_labels.copy_(b[2], non_blocking=True)
 
+    first_loss = None
     with torch.cuda.stream(stream):
         for i in range(max(3, args.warmup)):
             load_static(pool_d[i % args.pool])
             tr.step(s_ids, s_dense, s_labels)
+            if first_loss is None:
+                first_loss = float(tr.last_loss_sum()) / cfg.batch      # loss of the very first step (random init)
         stream.synchronize()
         say("eager warm-up done")
         host_barrier()
@@ -277,6 +283,7 @@ def main() -> int:
         dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t_dev[0]), float(t_dev[1])
     global_batch = cfg.batch * world
+    out = None
     if rank == 0:
         out = {
             "metric": "train examples/sec (device-timed, max over ranks)",
@@ -296,13 +303,50 @@ def main() -> int:
                              "mailbox) exceeds the 126 MB L2; ids change every step"},
             "e2e": {"value": global_batch * args.steps / (e2e_ms / 1e3), "unit": "examples/s",
                     "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4, "steps_per_graph": Ge,
-                    "last_loss": last_loss},
+                    "first_loss": first_loss, "last_loss": last_loss},
             "gpu_launches": int(launches_per_step) * args.steps,
             "gpu_launches_per_step": int(launches_per_step),
             "clocks": clocks,
         }
-        print(json.dumps(out))
     tr.close()
+
+    # ---------------- after the timed regions: correctness on the real ranks -----------------------------
+    # A small sync-replica job on the same ranks (fd-attached slabs, device barriers, NVLS when available)
+    # against the fp32 PyTorch oracle on rank 0 (models/wide_deep_verify.py).  It runs after the numbers are
+    # taken, under a watchdog that prints the line anyway, so it can never cost the measurement.
+    def emit(verify):
+        if rank == 0:
+            out["verify"] = verify
+            print(json.dumps(out), flush=True)
+
+    if os.environ.get("DTF_BENCH_VERIFY", "1") == "0":
+        emit({"ok": None, "skipped": "DTF_BENCH_VERIFY=0"})
+    else:
+        def bail():
+            emit({"ok": None, "error": "verify did not finish within %d s" % limit})
+            os._exit(0)
+        limit = int(os.environ.get("DTF_BENCH_VERIFY_TIMEOUT", "90"))
+        dog = threading.Timer(limit, bail)
+        dog.daemon = True
+        dog.start()
+        try:
+            from distributed_tensorflow_b200.models.wide_deep_verify import verify_multi_rank
+            verify = verify_multi_rank(rank, world, dev, dist if world > 1 else None)
+        except Exception as e:  # noqa: BLE001  (reported, never fatal for the measurement)
+            verify = {"ok": None, "error": "%s: %s" % (type(e).__name__, str(e)[:300])}
+            dog.cancel()
+            emit(verify)
+            os._exit(0)                              # peers may still sit in a collective: leave without teardown
+        dog.cancel()
+        emit(verify)
+        # ok == False with an error several times beyond the tolerance is a wrong result, not noise: fail the run
+        gross = verify.get("ok") is False and float(verify.get("max_rel_err") or 0.0) > float(os.environ.get("DTF_VERIFY_FAIL_AT", "5"))
+        if gross:
+            if rank == 0:
+                print("verify FAILED: %s" % json.dumps(verify), file=sys.stderr, flush=True)
+            if world > 1:
+                dist.destroy_process_group()
+            return 3
     if world > 1:
         dist.destroy_process_group()
     return 0

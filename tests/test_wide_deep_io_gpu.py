@@ -192,3 +192,41 @@ def test_survivor_exits_non_zero_when_its_peer_dies(tmp_path):
     assert procs["master"].returncode == 1, out
     assert "timed out waiting for rank 1" in out or "missing or dead" in out or "did not write their shard" in out, out
     assert time.time() - t0 < 90
+
+
+def test_verify_step_against_torch_oracle_single_rank():
+    """The check bench.py embeds in its JSON line (models/wide_deep_verify.py), one rank: product layer sizes,
+    26 slots, three sync steps held against the fp32 PyTorch restatement."""
+    from distributed_tensorflow_b200.models.wide_deep_verify import verify_multi_rank
+    v = verify_multi_rank(0, 1, torch.device("cuda", 0), None, steps=3)
+    assert v["steps"] == 3 and v["ranks"] == 1 and v["dense_copies_identical"]
+    assert v["max_rel_err"] < 5.0, v            # <= 1 is inside the unit-test tolerances; report the detail if not
+    assert v["ok"], v
+
+
+def test_verify_step_two_real_ranks(tmp_path):
+    """Same check on two real processes (torchrun): fd-attached slabs, device barriers, split-SM push."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = tmp_path / "v.py"
+    script.write_text(
+        "import os, json, torch, torch.distributed as dist\\n"
+        "from distributed_tensorflow_b200.models.wide_deep_verify import verify_multi_rank\\n"
+        "r, w = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])\\n"
+        "torch.cuda.set_device(r)\\n"
+        "dist.init_process_group('gloo', rank=r, world_size=w)\\n"
+        "v = verify_multi_rank(r, w, torch.device('cuda', r), dist)\\n"
+        "print('VERIFY ' + json.dumps(v)) if r == 0 else None\\n"
+        "dist.destroy_process_group()\\n")
+    env = dict(os.environ)
+    env["PYTHONPATH"] = REPO
+    env.pop("TF_CONFIG", None)
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", str(port), str(script)], cwd=str(tmp_path), env=env, capture_output=True,
+                       text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    import json
+    v = json.loads([l for l in p.stdout.splitlines() if l.startswith("VERIFY ")][0][7:])
+    assert v["ok"] and v["ranks"] == 2, v
