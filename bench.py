@@ -314,42 +314,70 @@ def main() -> int:
     # A small sync-replica job on the same ranks (fd-attached slabs, device barriers, NVLS when available)
     # against the fp32 PyTorch oracle on rank 0 (models/wide_deep_verify.py).  It runs after the numbers are
     # taken, under a watchdog that prints the line anyway, so it can never cost the measurement.
-    def emit(verify):
+    post = {"verify": None, "vs_torch_baseline": None}
+
+    def emit():
         if rank == 0:
-            out["verify"] = verify
+            out.update(post)
             print(json.dumps(out), flush=True)
 
+    limit = int(os.environ.get("DTF_BENCH_POST_TIMEOUT", "240"))
+
+    def bail():
+        for k in post:
+            if post[k] is None:
+                post[k] = {"ok": None, "error": "did not finish within %d s" % limit}
+        emit()
+        os._exit(0)
+    dog = threading.Timer(limit, bail)
+    dog.daemon = True
+    dog.start()
+
+    def fail_soft(key, e):
+        post[key] = {"ok": None, "error": "%s: %s" % (type(e).__name__, str(e)[:300])}
+        dog.cancel()
+        emit()
+        os._exit(0)                                  # peers may still sit in a collective: leave without teardown
+
     if os.environ.get("DTF_BENCH_VERIFY", "1") == "0":
-        emit({"ok": None, "skipped": "DTF_BENCH_VERIFY=0"})
+        post["verify"] = {"ok": None, "skipped": "DTF_BENCH_VERIFY=0"}
     else:
-        def bail():
-            emit({"ok": None, "error": "verify did not finish within %d s" % limit})
-            os._exit(0)
-        limit = int(os.environ.get("DTF_BENCH_VERIFY_TIMEOUT", "90"))
-        dog = threading.Timer(limit, bail)
-        dog.daemon = True
-        dog.start()
         try:
             from distributed_tensorflow_b200.models.wide_deep_verify import verify_multi_rank
-            verify = verify_multi_rank(rank, world, dev, dist if world > 1 else None)
+            post["verify"] = verify_multi_rank(rank, world, dev, dist if world > 1 else None)
         except Exception as e:  # noqa: BLE001  (reported, never fatal for the measurement)
-            verify = {"ok": None, "error": "%s: %s" % (type(e).__name__, str(e)[:300])}
-            dog.cancel()
-            emit(verify)
-            os._exit(0)                              # peers may still sit in a collective: leave without teardown
-        dog.cancel()
-        emit(verify)
-        # ok == False with an error several times beyond the tolerance is a wrong result, not noise: fail the run
-        gross = verify.get("ok") is False and float(verify.get("max_rel_err") or 0.0) > float(os.environ.get("DTF_VERIFY_FAIL_AT", "5"))
-        if gross:
-            if rank == 0:
-                print("verify FAILED: %s" % json.dumps(verify), file=sys.stderr, flush=True)
-            if world > 1:
-                dist.destroy_process_group()
-            return 3
+            fail_soft("verify", e)
+
+    # Same-box comparison arm: the PyTorch NCCL + cuBLAS baseline (baseline/wide_deep_torch.py, none of this
+    # repository's kernels) timed on the same ranks for the same mode, after our own numbers were taken.
+    # The contract's `vs_baseline` stays null (the reference publishes no number); this is a separate key.
+    if os.environ.get("DTF_BENCH_BASELINE", "1") == "0":
+        post["vs_torch_baseline"] = {"skipped": "DTF_BENCH_BASELINE=0"}
+    else:
+        try:
+            from baseline.wide_deep_torch import time_baseline
+            grp = dist.new_group(backend="nccl") if world > 1 else None
+            r = time_baseline(args, rank, world, dev, group=grp, mode=args.mode, steps=min(args.steps, 20))
+            base_value = global_batch / (r["ms_per_step"] / 1e3)
+            post["vs_torch_baseline"] = {
+                "impl": "torch-nccl-cublas (fixed-capacity all_to_all, flat bf16 all-reduce, CUDA graph)",
+                "value": base_value, "unit": "examples/s", "ms_per_step": r["ms_per_step"], "steps": r["steps"],
+                "ratio": (out["value"] / base_value) if rank == 0 else None,
+                "e2e_ratio": (out["e2e"]["value"] / (global_batch / (r["e2e_ms_per_step"] / 1e3))) if rank == 0 else None,
+                "cuda_graph": r["cuda_graph"], "why_eager": r["why_eager"], "dropped_ids": r["dropped_ids"],
+                "first_loss": r["first_loss"], "last_loss": r["last_loss"]}
+        except Exception as e:  # noqa: BLE001
+            fail_soft("vs_torch_baseline", e)
+    dog.cancel()
+    emit()
+    verify = post["verify"] or {}
+    # ok == False with an error several times beyond the tolerance is a wrong result, not noise: fail the run
+    gross = verify.get("ok") is False and float(verify.get("max_rel_err") or 0.0) > float(os.environ.get("DTF_VERIFY_FAIL_AT", "5"))
+    if gross and rank == 0:
+        print("verify FAILED: %s" % json.dumps(verify), file=sys.stderr, flush=True)
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 3 if gross else 0
 
 
 if __name__ == "__main__":
