@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """``python -m auto_stop_ps.task`` -- trainer.task plus "ps tasks exit once every worker and the
 master are done" (interface of /root/reference/auto_stop_ps/task.py; ``max_epochs`` defaults to 20
-there, :18).  Like the reference, this directory is a namespace module (no ``__init__.py``)."""
+there, :18).  The reference ships this directory without an ``__init__.py`` (a namespace module); here it has one so that setup.py can list it as a package."""
 from distributed_tensorflow_b200 import flags, trainer_lib
 from distributed_tensorflow_b200.extra_flags import define as _define_extra
 

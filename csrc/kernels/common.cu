@@ -139,4 +139,11 @@ void dtf_reset_launch_count(void) { dtf::g_launches.store(0, std::memory_order_r
 
 int dtf_kernels_abi_version(void) { return DTF_KERNELS_ABI_VERSION; }
 
+// sha256 over csrc/kernels + include at build time (utils/build.py passes it in): lets build() and the
+// loader tell a library that was built from other sources than the ones in the tree
+#ifndef DTF_SOURCE_HASH
+#define DTF_SOURCE_HASH "unstamped"
+#endif
+const char* dtf_kernels_source_hash(void) { return DTF_SOURCE_HASH; }
+
 }  // extern "C"

@@ -137,6 +137,17 @@ class WideDeepTrainer:
             raise _lib.KernelError("dtf_wd_create: " + self._L.dtf_last_error().decode())
         self.info = _CInfo()
         self._L.dtf_wd_info(self._h, C.byref(self.info))
+        # The partitioning rule has one statement in Python (placement.RowShard / RangeShard: what checkpoints,
+        # export, serving and the tests use to address shards) and one in the C++ executor that lays the
+        # buffers out; a disagreement would silently mis-assemble every checkpoint, so it is fatal here.
+        from ..placement import RangeShard, RowShard
+        self.row_shard = RowShard(rows=cfg.emb_rows, world=world)
+        self.dense_shard = RangeShard(n=int(self.info.P_pad), world=world, align=256)
+        if (self.row_shard.local_rows(rank) != self.info.rows_local
+                or self.dense_shard.bounds(rank) != (self.info.dense_lo, self.info.dense_hi)):
+            raise _lib.KernelError("placement mismatch between placement.py and the C++ plan: rows %d vs %d, dense %s vs %s"
+                                   % (self.row_shard.local_rows(rank), self.info.rows_local, self.dense_shard.bounds(rank),
+                                      (self.info.dense_lo, self.info.dense_hi)))
         self._attached = world == 1
         self._views: Dict[str, torch.Tensor] = {}
         # loss accumulators live after cnt[16] + counter[4] in the per-step scratch (one per parity)

@@ -22,10 +22,15 @@ def assemble(variables: Dict[str, np.ndarray], name: str, world: int) -> np.ndar
     parts = [variables["%s/part_%d" % (name, r)] for r in range(world)]
     if name == "dense_flat":
         return np.concatenate(parts)
+    from ..placement import RowShard
     rows = sum(p.shape[0] for p in parts)
+    shard = RowShard(rows=rows, world=world)
     out = np.empty((rows,) + parts[0].shape[1:], dtype=parts[0].dtype)
     for r, p in enumerate(parts):
-        out[r::world] = p
+        if p.shape[0] != shard.local_rows(r):
+            raise ValueError("%s/part_%d has %d rows, the row sharding of %d rows over %d ranks gives it %d"
+                             % (name, r, p.shape[0], rows, world, shard.local_rows(r)))
+        out[shard.global_row(r, 0)::world] = p          # local row l of rank r is global row l * world + r
     return out
 
 

@@ -20,9 +20,11 @@ class KernelError(RuntimeError):
 def lib() -> ctypes.CDLL:
     global _LIB
     if _LIB is None:
-        if not _PATH.exists():
-            from ..utils.build import build_kernels
-            build_kernels()
+        from ..utils import build as _build
+        # (re)build when the library is missing or was built from other sources than the tree holds
+        # (content hash of csrc/kernels + include, stamped next to the .so and compiled into it)
+        if not _PATH.exists() or _build.built_hash(_PATH) != _build.source_hash("kernels"):
+            _build.build_kernels()
         L = ctypes.CDLL(str(_PATH))
         L.dtf_last_error.restype = ctypes.c_char_p
         L.dtf_launch_count.restype = ctypes.c_longlong

@@ -57,7 +57,9 @@ def replica_device_setter(cluster: ClusterSpec = None, worker_device: str = "/jo
 
 @dataclass(frozen=True)
 class RowShard:
-    """Row ``r`` of a [rows, dim] table lives on rank ``r % world`` at local row ``r // world``."""
+    """Row ``r`` of a [rows, dim] table lives on rank ``r % world`` at local row ``r // world``.
+    Used by the GPU trainer (cross-checked against the C++ plan's layout at construction), by the serving
+    loader that re-assembles exported shards, and by the multi-rank verify step."""
     rows: int
     world: int
 

@@ -73,22 +73,54 @@ def _compile_all(srcs: list[Path], mk_cmd, tag: str, jobs: int) -> list[Path]:
     return objs
 
 
+def source_hash(subdir: str) -> str:
+    """sha256 over the names and contents of csrc/<subdir>/* and include/*.h."""
+    import hashlib
+    h = hashlib.sha256()
+    files = sorted(p for p in (CSRC / subdir).iterdir() if p.is_file()) + sorted((REPO / "include").glob("*.h"))
+    for p in files:
+        h.update(p.name.encode() + b"\0")
+        h.update(p.read_bytes())
+        h.update(b"\0")
+    return h.hexdigest()[:32]
+
+
+def _stamp_path(out: Path) -> Path:
+    return out.with_suffix(out.suffix + ".srchash")
+
+
+def built_hash(out: Path) -> str:
+    p = _stamp_path(out)
+    return p.read_text().strip() if p.exists() and out.exists() else ""
+
+
 def build_kernels(force: bool = False, jobs: int | None = None, verbose: bool = False) -> Path:
-    """Compile csrc/kernels/*.cu -> _lib/libdtf_kernels.so (sm_100a)."""
+    """Compile csrc/kernels/*.cu -> _lib/libdtf_kernels.so (sm_100a).
+
+    Objects are cached by mtime for quick edits, but the library as a whole is tied to a content hash of
+    ``csrc/kernels`` + ``include``: when the hash stamped next to (and compiled into) the existing library
+    differs from the tree's, everything is rebuilt from scratch, so a prebuilt ``.so`` that travelled with
+    a snapshot can never silently stand in for different sources."""
     srcs = sorted((CSRC / "kernels").glob("*.cu"))
     out = LIB_DIR / "libdtf_kernels.so"
     LIB_DIR.mkdir(parents=True, exist_ok=True)
+    want = source_hash("kernels")
+    if built_hash(out) != want:
+        force = True
     if force and OBJ_DIR.exists():
         for o in OBJ_DIR.glob("k_*.o"):
             o.unlink()
     nvcc = _nvcc()
     extra = ["-Xptxas", "-v"] if verbose else []
-    objs = _compile_all(
-        srcs, lambda s, o: [nvcc, *NVCC_FLAGS, *extra, "-I", str(REPO / "include"), "-c", str(s), "-o", str(o)],
-        "k", jobs or min(8, os.cpu_count() or 4))
+
+    def cmd(s, o):
+        stamp = ["-DDTF_SOURCE_HASH=\"%s\"" % want] if s.name == "common.cu" else []
+        return [nvcc, *NVCC_FLAGS, *extra, *stamp, "-I", str(REPO / "include"), "-c", str(s), "-o", str(o)]
+    objs = _compile_all(srcs, cmd, "k", jobs or min(8, os.cpu_count() or 4))
     if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
         _run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static",
               "-Xcompiler", "-fPIC", "-o", str(out), *map(str, objs), "-lpthread", "-ldl", "-lrt"])
+    _stamp_path(out).write_text(want + "\n")
     return out
 
 
@@ -97,6 +129,9 @@ def build_native(force: bool = False, jobs: int | None = None) -> Path:
     srcs = [p for p in sorted((CSRC / "native").glob("*.cc")) if p.name != "tsan_stress.cc"]   # that one has a main()
     out = LIB_DIR / "libdtf_native.so"
     LIB_DIR.mkdir(parents=True, exist_ok=True)
+    want = source_hash("native")
+    if built_hash(out) != want:
+        force = True                       # same rule as the kernels: the library follows the content of its sources
     if force and OBJ_DIR.exists():
         for o in OBJ_DIR.glob("n_*.o"):
             o.unlink()
@@ -106,6 +141,7 @@ def build_native(force: bool = False, jobs: int | None = None) -> Path:
         "n", jobs or min(8, os.cpu_count() or 4))
     if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
         _run([cxx, "-shared", "-pthread", "-o", str(out), *map(str, objs)])
+    _stamp_path(out).write_text(want + "\n")
     return out
 
 

@@ -24,6 +24,7 @@ const char* dtf_last_error(void);
 long long dtf_launch_count(void);      /* kernels launched by this library since the last reset */
 void dtf_reset_launch_count(void);
 int dtf_kernels_abi_version(void);
+const char* dtf_kernels_source_hash(void);   /* hash of the sources this library was built from */
 
 /* ---- epilogues of dtf_gemm_bf16 -------------------------------------------------------------- */
 enum {
