@@ -77,6 +77,7 @@ struct Mapping {
   size_t size = 0;   // rounded to the granularity
   bool vmm = false;  // false: legacy cudaMalloc allocation
   bool imported = false;
+  bool owns_handle = true;   // false: the handle belongs to a multicast object (released by dtf_mc_destroy)
 };
 std::mutex g_mu;
 std::map<void*, Mapping> g_maps;
@@ -173,7 +174,7 @@ int dtf_symm_free(void* ptr) {
   Drv& d = drv();
   d.Unmap(reinterpret_cast<CUdeviceptr>(ptr), m.size);
   d.AddressFree(reinterpret_cast<CUdeviceptr>(ptr), m.size);
-  d.Release(m.handle);
+  if (m.owns_handle) d.Release(m.handle);
   return 0;
 }
 
@@ -249,6 +250,7 @@ namespace {
 struct McObject {
   CUmemGenericAllocationHandle handle = 0;
   size_t bytes = 0;
+  void* mapping = nullptr;   // this process's mapping of the object (dtf_mc_bind_map)
 };
 std::map<long long, McObject> g_mc;
 long long g_mc_next = 1;
@@ -395,9 +397,30 @@ int dtf_mc_bind_map(long long id, void* slab, void** mc_ptr_out) {
   if (map_handle(o.handle, o.bytes, dev, &p) != 0) return -1;
   {
     std::lock_guard<std::mutex> l(g_mu);
-    g_maps[p] = Mapping{o.handle, o.bytes, true, true};
+    g_maps[p] = Mapping{o.handle, o.bytes, true, true, /*owns_handle=*/false};
+    g_mc[id].mapping = p;
   }
   *mc_ptr_out = p;
+  return 0;
+}
+
+// Tear one multicast object down exactly once: unmap this process's view of it (if it was mapped) and
+// release the object handle.  The slabs bound to it stay valid; the driver drops the bindings with the
+// last reference to the object.
+int dtf_mc_destroy(long long id) {
+  McObject o;
+  {
+    std::lock_guard<std::mutex> l(g_mu);
+    auto it = g_mc.find(id);
+    if (it == g_mc.end()) {
+      set_error("multicast: unknown object %lld", id);
+      return -2;
+    }
+    o = it->second;
+    g_mc.erase(it);
+  }
+  if (o.mapping != nullptr) dtf_symm_free(o.mapping);   // unmaps only: the mapping does not own the handle
+  drv().Release(o.handle);
   return 0;
 }
 

@@ -259,6 +259,7 @@ class WideDeepTrainer:
                 L.dtf_wd_attach_multicast(self._h, None, 0)
                 return
             self.multicast = True
+            self._mc_id = int(mc_id.value)
 
     def attach_local(self, peers: List["WideDeepTrainer"]) -> None:
         """Peers living in this process (several ranks emulated on one device, or one process
@@ -468,6 +469,12 @@ class WideDeepTrainer:
     def close(self) -> None:
         if self._h:
             self._views.clear()
+            if getattr(self, "_mc_id", None) is not None and os.environ.get("DTF_MC_DESTROY", "0") == "1":
+                # explicit teardown of the NVLS object (unmap + release, once); by default it is left to process exit
+                self._L.dtf_wd_attach_multicast(self._h, None, 0)
+                self._L.dtf_mc_destroy.argtypes = [C.c_longlong]
+                self._L.dtf_mc_destroy(self._mc_id)
+                self._mc_id = None
             self._L.dtf_wd_destroy(self._h)
             self._h = None
 

@@ -140,6 +140,7 @@ int dtf_mc_create(int num_devices, size_t bytes, long long* id_out, int* fd_out)
 int dtf_mc_import(int fd, size_t bytes, long long* id_out);
 int dtf_mc_add_device(long long id);
 int dtf_mc_bind_map(long long id, void* slab, void** mc_ptr_out);
+int dtf_mc_destroy(long long id);   /* unmap this process's view and release the object, exactly once */
 
 /* ---- wide-and-deep plan: the training / serving step executor -------------------------------- *
  * Every rank is a worker and a parameter-server shard at once (embedding row r on rank
