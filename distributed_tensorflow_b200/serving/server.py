@@ -196,6 +196,18 @@ class _FastJson:
 def make_http_server(model: ModelServer, host: str = "0.0.0.0", port: int = 8500) -> ThreadingHTTPServer:
     class Handler(BaseHTTPRequestHandler):
         protocol_version = "HTTP/1.1"
+        # Response head and body must leave in ONE segment on keep-alive connections: with an unbuffered wfile
+        # the body is a second small write that Nagle holds back until the client's delayed ACK (40 ms) -- measured
+        # 44 ms per request for any body under ~1 MB.  Buffered writes (flushed once per request) + TCP_NODELAY.
+        wbufsize = 1 << 20
+
+        def setup(self):
+            super().setup()
+            try:
+                import socket as _socket
+                self.connection.setsockopt(_socket.IPPROTO_TCP, _socket.TCP_NODELAY, 1)
+            except OSError:
+                pass
 
         def _send(self, code: int, payload: dict) -> None:
             self._send_raw(code, json.dumps(payload).encode())
