@@ -85,6 +85,28 @@ def source_hash(subdir: str) -> str:
     return h.hexdigest()[:32]
 
 
+class _BuildLock:
+    """Inter-process lock around a build: several tasks of one job start at the same moment (ps, worker,
+    master, or N torchrun ranks) and each checks the libraries; without the lock two of them could decide to
+    rebuild at once and delete each other's objects, or load a library that another one is relinking."""
+
+    def __init__(self, name: str):
+        LIB_DIR.mkdir(parents=True, exist_ok=True)
+        self.path = LIB_DIR / (name + ".lock")
+        self.f = None
+
+    def __enter__(self):
+        import fcntl
+        self.f = open(self.path, "w")
+        fcntl.flock(self.f, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *a):
+        import fcntl
+        fcntl.flock(self.f, fcntl.LOCK_UN)
+        self.f.close()
+
+
 def _stamp_path(out: Path) -> Path:
     return out.with_suffix(out.suffix + ".srchash")
 
@@ -101,6 +123,11 @@ def build_kernels(force: bool = False, jobs: int | None = None, verbose: bool = 
     ``csrc/kernels`` + ``include``: when the hash stamped next to (and compiled into) the existing library
     differs from the tree's, everything is rebuilt from scratch, so a prebuilt ``.so`` that travelled with
     a snapshot can never silently stand in for different sources."""
+    with _BuildLock("kernels"):
+        return _build_kernels_locked(force, jobs, verbose)
+
+
+def _build_kernels_locked(force: bool, jobs, verbose: bool) -> Path:
     srcs = sorted((CSRC / "kernels").glob("*.cu"))
     out = LIB_DIR / "libdtf_kernels.so"
     LIB_DIR.mkdir(parents=True, exist_ok=True)
@@ -118,14 +145,21 @@ def build_kernels(force: bool = False, jobs: int | None = None, verbose: bool = 
         return [nvcc, *NVCC_FLAGS, *extra, *stamp, "-I", str(REPO / "include"), "-c", str(s), "-o", str(o)]
     objs = _compile_all(srcs, cmd, "k", jobs or min(8, os.cpu_count() or 4))
     if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
+        tmp = out.with_suffix(".so.tmp%d" % os.getpid())
         _run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static",
-              "-Xcompiler", "-fPIC", "-o", str(out), *map(str, objs), "-lpthread", "-ldl", "-lrt"])
+              "-Xcompiler", "-fPIC", "-o", str(tmp), *map(str, objs), "-lpthread", "-ldl", "-lrt"])
+        os.replace(tmp, out)                 # readers never see a half-written library
     _stamp_path(out).write_text(want + "\n")
     return out
 
 
 def build_native(force: bool = False, jobs: int | None = None) -> Path:
     """Compile csrc/native/*.cc -> _lib/libdtf_native.so (CPU runtime)."""
+    with _BuildLock("native"):
+        return _build_native_locked(force, jobs)
+
+
+def _build_native_locked(force: bool, jobs) -> Path:
     srcs = [p for p in sorted((CSRC / "native").glob("*.cc")) if p.name != "tsan_stress.cc"]   # that one has a main()
     out = LIB_DIR / "libdtf_native.so"
     LIB_DIR.mkdir(parents=True, exist_ok=True)
@@ -140,7 +174,9 @@ def build_native(force: bool = False, jobs: int | None = None) -> Path:
         srcs, lambda s, o: [cxx, *CXX_FLAGS, "-I", str(REPO / "include"), "-c", str(s), "-o", str(o)],
         "n", jobs or min(8, os.cpu_count() or 4))
     if force or not out.exists() or any(o.stat().st_mtime > out.stat().st_mtime for o in objs):
-        _run([cxx, "-shared", "-pthread", "-o", str(out), *map(str, objs)])
+        tmp = out.with_suffix(".so.tmp%d" % os.getpid())
+        _run([cxx, "-shared", "-pthread", "-o", str(tmp), *map(str, objs)])
+        os.replace(tmp, out)
     _stamp_path(out).write_text(want + "\n")
     return out
 
