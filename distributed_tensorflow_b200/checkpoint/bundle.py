@@ -70,6 +70,7 @@ class BundleReader:
         self.prefix = prefix
         self.num_shards = int(self._L.dtfn_bundle_reader_num_shards(self._h))
         self._entries: Dict[str, Tuple[int, int, Tuple[int, ...], int, int, int, int]] = {}
+        self._slice_entries: Dict[bytes, Tuple[int, int, Tuple[int, ...], int, int, int, int]] = {}
         n = int(self._L.dtfn_bundle_reader_count(self._h))
         name_p, name_n = C.c_void_p(), C.c_size_t()
         dtype, ndims, shard = C.c_int(), C.c_int(), C.c_int()
@@ -80,9 +81,14 @@ class BundleReader:
                                                   C.byref(ndims), dims, C.byref(shard), C.byref(off), C.byref(size),
                                                   C.byref(crc))
             _native.check(rc, "bundle entry")
-            name = C.string_at(name_p.value, name_n.value).decode()
-            self._entries[name] = (i, dtype.value, tuple(dims[d] for d in range(ndims.value)), shard.value,
-                                   off.value, size.value, crc.value)
+            raw = C.string_at(name_p.value, name_n.value)
+            rec = (i, dtype.value, tuple(dims[d] for d in range(ndims.value)), shard.value, off.value, size.value, crc.value)
+            if raw[:1] == b"\x00":
+                # slice of a partitioned variable, stored under an OrderedCode key (TF's EncodeTensorNameSlice);
+                # reached through the full tensor's entry, not by name
+                self._slice_entries[raw] = rec
+                continue
+            self._entries[raw.decode()] = rec
 
     def keys(self) -> List[str]:
         return list(self._entries)
@@ -93,6 +99,10 @@ class BundleReader:
     def entry(self, name: str) -> dict:
         i, dt, shape, shard, off, size, crc = self._entries[name]
         return {"dtype": dt, "shape": shape, "shard_id": shard, "offset": off, "size": size, "crc32c": crc}
+
+    def num_slices(self, name: str) -> int:
+        """> 0 when ``name`` is a partitioned variable stored as slices (``get_tensor`` assembles them)."""
+        return int(self._L.dtfn_bundle_reader_num_slices(self._h, self._entries[name][0]))
 
     def get_variable_to_shape_map(self) -> Dict[str, Tuple[int, ...]]:
         return {k: v[2] for k, v in self._entries.items()}

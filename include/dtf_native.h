@@ -66,6 +66,9 @@ int dtfn_bundle_reader_entry(const dtfn_bundle_reader*, long long i, const char*
                              long long* size, uint32_t* masked_crc);
 int dtfn_bundle_reader_lookup(const dtfn_bundle_reader*, const char* name);  /* index or -1 */
 int dtfn_bundle_reader_read(const dtfn_bundle_reader*, long long i, void* dst, size_t nbytes);  /* crc checked */
+/* > 0: entry i is the full tensor of a partitioned variable (BundleEntryProto.slices); reading it assembles
+ * the slices, which live under OrderedCode-encoded keys (start with a zero byte) next to the tensor names */
+int dtfn_bundle_reader_num_slices(const dtfn_bundle_reader*, long long i);
 void dtfn_bundle_reader_close(dtfn_bundle_reader*);
 
 /* ---- TFRecord framing (event files) -------------------------------------------------------- *

@@ -190,3 +190,66 @@ def test_event_file_framing_and_tensorboard_loader(tmp_path):
     assert events[0].file_version == "brain.Event:2" and events[1].HasField("graph_def")
     got = [(e.step, v.tag, v.simple_value) for e in events for v in e.summary.value]
     assert got == [(100, "loss", 1.5), (100, "training/hptuning/metric", 1.5), (200, "loss", 0.25)]
+
+
+def test_merged_partitions_also_appear_as_one_tf_style_partitioned_variable(tmp_path):
+    """``<var>/part_<r>`` entries written by the ranks are, after the merge, ALSO reachable the way TensorFlow stores a
+    PartitionedVariable: an entry for the full tensor that lists its slices (BundleEntryProto.slices) plus one entry
+    per slice under an OrderedCode key (EncodeTensorNameSlice), pointing at the same bytes -- no data is duplicated.
+    Golden bytes of the keys are derived by hand from ordered_code.cc (no TensorFlow on this box to produce them)."""
+    rng = np.random.RandomState(3)
+    parts = [rng.randn(n, 4).astype(np.float32) for n in (3, 2, 2)]
+    accs = [np.full((p.shape[0], 4), 0.1 + r, np.float32) for r, p in enumerate(parts)]
+    dense = [np.arange(5, dtype=np.float32) + 10 * r for r in range(3)]
+    prefixes = []
+    for r in range(3):
+        p = str(tmp_path / ("part-%05d" % r))
+        t = {"embedding/part_%d" % r: parts[r], "embedding/part_%d/Adagrad" % r: accs[r], "dense_flat/part_%d" % r: dense[r]}
+        if r == 0:
+            t["global_step"] = np.array(7, np.int64)
+        B.write_bundle(p, t)
+        prefixes.append(p)
+    m = str(tmp_path / "model.ckpt-7")
+    size_before = sum(os.path.getsize(p + ".data-00000-of-00001") for p in prefixes)
+    B.merge_bundles(prefixes, m)
+    assert sum(os.path.getsize("%s.data-%05d-of-00003" % (m, r)) for r in range(3)) == size_before
+    with B.BundleReader(m) as r:
+        keys = r.keys()
+        assert {"embedding", "embedding/Adagrad", "dense_flat", "embedding/part_0", "embedding/part_2/Adagrad", "global_step"} <= set(keys)
+        assert r.num_slices("embedding") == 3 and r.num_slices("embedding/part_1") == 0 and r.num_slices("global_step") == 0
+        assert r.get_variable_to_shape_map()["embedding"] == (7, 4) and r.get_variable_to_shape_map()["dense_flat"] == (15,)
+        assert np.array_equal(r.get_tensor("embedding"), np.concatenate(parts))          # assembled from the slices
+        assert np.array_equal(r.get_tensor("embedding/Adagrad"), np.concatenate(accs))
+        assert np.array_equal(r.get_tensor("dense_flat"), np.concatenate(dense))
+        assert np.array_equal(r.get_tensor("embedding/part_1"), parts[1])                 # the per-rank names still work
+        # slice keys: 00 | "embedding" 00 01 | 01 02 (two dims) | start, length of dim 0 | 0x80 (start 0), 0x7f (length -1)
+        want = [b"\x00embedding\x00\x01\x01\x02" + bytes([0x80 + s, 0x80 + n]) + b"\x80\x7f" for s, n in ((0, 3), (3, 2), (5, 2))]
+        assert sorted(r._slice_entries) == sorted(want + [k.replace(b"embedding", b"embedding/Adagrad") for k in want]
+                                                  + [b"\x00dense_flat\x00\x01\x01\x01" + bytes([0x80 + 5 * i, 0x85]) for i in range(3)])
+        e = r._slice_entries[want[1]]
+        assert (e[3], e[4], e[5]) == tuple(r.entry("embedding/part_1")[k] for k in ("shard_id", "offset", "size"))
+    # a single partition is simply a second name for the same bytes
+    p = str(tmp_path / "solo")
+    B.write_bundle(p, {"embedding/part_0": parts[0]})
+    B.merge_bundles([p], str(tmp_path / "solo.ckpt"))
+    with B.BundleReader(str(tmp_path / "solo.ckpt")) as r:
+        assert r.num_slices("embedding") == 0 and np.array_equal(r.get_tensor("embedding"), parts[0])
+
+
+def test_ordered_code_signed_numbers_longer_than_one_byte(tmp_path):
+    """Row offsets of real shards need the multi-byte form of WriteSignedNumIncreasing: 1 250 000 = 0x1312d0 has 21
+    significant bits -> 4 bytes, header 0xf0 XORed onto the big-endian value: f0 13 12 d0; 64 -> c0 40; 8127 -> df bf."""
+    parts = [np.zeros((1250000, 1), np.int8), np.zeros((64, 1), np.int8), np.zeros((8191 - 64, 1), np.int8), np.ones((5, 1), np.int8)]
+    prefixes = []
+    for r, a in enumerate(parts):
+        p = str(tmp_path / ("p%d" % r))
+        B.write_bundle(p, {"t/part_%d" % r: a})
+        prefixes.append(p)
+    B.merge_bundles(prefixes, str(tmp_path / "m"))
+    with B.BundleReader(str(tmp_path / "m")) as r:
+        keys = sorted(r._slice_entries)
+        head = b"\x00t\x00\x01\x01\x02"
+        assert head + b"\x80" + b"\xf0\x13\x12\xd0" + b"\x80\x7f" in keys                      # start 0, length 1 250 000
+        assert head + b"\xf0\x13\x12\xd0" + b"\xc0\x40" + b"\x80\x7f" in keys                  # start 1 250 000, length 64
+        assert head + b"\xf0\x13\x13\x10" + b"\xdf\xbf" + b"\x80\x7f" in keys                  # start 1 250 064, length 8127 = 0x1fbf
+        assert int(r.get_tensor("t").sum()) == 5 and r.get_tensor("t").shape == (1250000 + 8191 + 5, 1)

@@ -67,6 +67,10 @@ def test_three_processes_from_tf_config_train_checkpoint_export_and_ps_auto_stop
         assert {"embedding/part_0", "embedding/part_1", "embedding/part_1/Adagrad", "global_step"} <= set(keys)
         step = int(r.get_tensor("global_step"))
         e0, e1 = r.get_tensor("embedding/part_0"), r.get_tensor("embedding/part_1")
+        # the same bytes as one TF-style partitioned variable (slices along dimension 0)
+        assert r.num_slices("embedding") == 2 and r.get_tensor("embedding").shape == (101, 128)
+        assert np.array_equal(r.get_tensor("embedding")[:51], e0) and np.array_equal(r.get_tensor("embedding/Adagrad")[51:],
+                                                                                     r.get_tensor("embedding/part_1/Adagrad"))
     assert 0 <= step <= 80 and e0.shape == (51, 128) and e1.shape == (50, 128)
     assert e0[0, 0] >= 1.0 and e1[0, 0] >= 2.0                   # rank-specific init, then +0.5 per step
     first = sorted(f for f in os.listdir(os.path.join(tmp, "ckpt")) if f.endswith(".index"))
