@@ -101,14 +101,27 @@ def latest_checkpoint(checkpoint_dir: str, latest_filename: str = None) -> Optio
 
 
 # ------------------------------------------------------------------------------ meta graph
-def _write_meta(path: str, var_names: List[str], sharded: bool, max_to_keep: int) -> None:
-    """``<prefix>.meta``: a MetaGraphDef carrying the saver_def (enough for tooling that inspects it;
-    restore never needs it)."""
+def _write_meta(path: str, var_names: List[str], sharded: bool, max_to_keep: int, model=None, tensors=None) -> None:
+    """``<prefix>.meta``: the MetaGraphDef ``tf.train.Saver`` writes next to every checkpoint.  With a model
+    description (the store's ``model``) it holds the model's graph in TF-1 layout with the saver sub-graph the
+    saver_def names and the ``variables`` / ``trainable_variables`` collections (``export/graph_def.py``), i.e.
+    what ``tf.train.import_meta_graph`` reads; without one, a bare variable list.  Restore never needs it."""
     try:
         from tensorboard.compat.proto import meta_graph_pb2, saver_pb2
     except Exception:  # tensorboard missing: the .meta file is optional
         return
     mg = meta_graph_pb2.MetaGraphDef()
+    if model is not None:
+        try:
+            from ..export.graph_def import fill_meta_graph
+            shapes = {k: (np.broadcast_to(np.zeros((), np.asarray(v).dtype), np.asarray(v).shape) if np.asarray(v).size > 16 else np.asarray(v))
+                      for k, v in (tensors or {}).items()}
+            fill_meta_graph(mg, model, shapes, sharded=sharded, max_to_keep=max_to_keep)
+            with open(path, "wb") as f:
+                f.write(mg.SerializeToString())
+            return
+        except Exception:  # noqa: BLE001  (fall back to the bare form below)
+            mg = meta_graph_pb2.MetaGraphDef()
     mg.meta_info_def.tensorflow_version = "1.15.0"
     mg.meta_info_def.tags.append("train")
     sd = mg.saver_def
@@ -170,12 +183,13 @@ class Saver:
                 pass
             with _bundle.BundleReader(prefix) as r:
                 names = r.keys()
+                tensors = {k: r.get_tensor(k) for k in names if int(np.prod(r.get_variable_to_shape_map()[k])) <= 16}
         else:
             tensors = self._filter(store.snapshot())
             _bundle.write_bundle(prefix, tensors)
             names = sorted(tensors)
         if self.write_meta_graph:
-            _write_meta(prefix + ".meta", names, self.sharded, self.max_to_keep)
+            _write_meta(prefix + ".meta", names, self.sharded, self.max_to_keep, getattr(store, "model", None), tensors)
         if prefix in self._last_checkpoints:
             self._last_checkpoints.remove(prefix)
         self._last_checkpoints.append(prefix)

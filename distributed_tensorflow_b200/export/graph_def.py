@@ -191,3 +191,43 @@ def graph_def_text(graph_def) -> str:
     """Text form, as ``tf.train.write_graph(..., 'graph.pbtxt')`` writes it."""
     from google.protobuf import text_format
     return text_format.MessageToString(graph_def)
+
+
+def variable_def_bytes(name: str, trainable: bool) -> bytes:
+    """Serialized ``VariableDef`` (tensorflow/core/framework/variable.proto), the items of the ``variables`` /
+    ``trainable_variables`` collections that ``tf.train.import_meta_graph`` turns back into Variable objects:
+    variable_name = 1, initializer_name = 2, snapshot_name = 3, initial_value_name = 6, trainable = 7."""
+    def field(num: int, text: str) -> bytes:
+        b = text.encode()
+        assert len(b) < 128
+        return bytes([(num << 3) | 2, len(b)]) + b
+    out = field(1, name + ":0") + field(2, name + "/Assign") + field(3, name + "/read:0") + field(6, name + "/initial_value:0")
+    if trainable:
+        out += bytes([(7 << 3) | 0, 1])
+    return out
+
+
+def fill_meta_graph(mg, model, tensors: Optional[Dict[str, np.ndarray]], tags=("train",), sharded: bool = True,
+                    max_to_keep: int = 5) -> None:
+    """MetaGraphDef as ``Saver.save`` writes it next to a checkpoint (``<prefix>.meta``): the model's graph with the
+    saver sub-graph, a saver_def that names nodes of that graph, and the variable collections."""
+    from tensorboard.compat.proto import saver_pb2
+    mg.meta_info_def.tensorflow_version = "1.15.0"
+    mg.meta_info_def.tensorflow_git_version = "distributed_tensorflow_b200"
+    mg.meta_info_def.tags.extend(tags)
+    names = build_graph_def(mg.graph_def, model, tensors)
+    mg.graph_def.versions.producer = 134
+    sd = mg.saver_def
+    sd.filename_tensor_name = names["filename_tensor_name"]
+    sd.save_tensor_name = names["save_tensor_name"]
+    sd.restore_op_name = names["restore_op_name"]
+    sd.max_to_keep = max_to_keep
+    sd.sharded = sharded
+    sd.keep_checkpoint_every_n_hours = 10000.0
+    sd.version = saver_pb2.SaverDef.V2
+    trainable = set(getattr(model, "trainable_names", lambda: [])())
+    var_nodes = [n.name for n in mg.graph_def.node if n.op == "VariableV2"]
+    for n in var_nodes:
+        mg.collection_def["variables"].bytes_list.value.append(variable_def_bytes(n, n in trainable))
+        if n in trainable:
+            mg.collection_def["trainable_variables"].bytes_list.value.append(variable_def_bytes(n, True))

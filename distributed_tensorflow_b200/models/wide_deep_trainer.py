@@ -188,6 +188,16 @@ class WideDeepCheckpointer:
         except OSError:
             pass
         s = self._saver
+        try:
+            # <prefix>.meta like tf.train.Saver: graph (placeholders, one VariableV2 per saved tensor, saver sub-graph),
+            # saver_def, variable collections -- shapes only, no tensor is loaded for it
+            from ..checkpoint.saver import _write_meta
+            with _bundle.BundleReader(prefix) as r:
+                dtypes = {k: _bundle.TF_TO_DTYPE.get(r.entry(k)["dtype"], np.dtype(np.float32)) for k in r.keys()}
+                shapes = {k: np.broadcast_to(np.zeros((), dtypes[k]), shp) for k, shp in r.get_variable_to_shape_map().items()}
+            _write_meta(prefix + ".meta", sorted(shapes), True, s.max_to_keep, WideDeepServingSpec(self.tr.export_config()), shapes)
+        except Exception as e:  # noqa: BLE001  (the .meta file is optional; restore never reads it)
+            print("checkpoint %s: no .meta written (%s)" % (prefix, e))
         s._last_checkpoints.append(prefix)
         while len(s._last_checkpoints) > s.max_to_keep:
             s._delete(s._last_checkpoints.pop(0))

@@ -253,3 +253,33 @@ def test_ordered_code_signed_numbers_longer_than_one_byte(tmp_path):
         assert head + b"\xf0\x13\x12\xd0" + b"\xc0\x40" + b"\x80\x7f" in keys                  # start 1 250 000, length 64
         assert head + b"\xf0\x13\x13\x10" + b"\xdf\xbf" + b"\x80\x7f" in keys                  # start 1 250 064, length 8127 = 0x1fbf
         assert int(r.get_tensor("t").sum()) == 5 and r.get_tensor("t").shape == (1250000 + 8191 + 5, 1)
+
+
+def test_meta_file_next_to_a_checkpoint_is_an_importable_meta_graph(tmp_path):
+    """``model.ckpt-N.meta`` (reference trainer/task.py:143,215-223: Saver handed to the Supervisor): graph with the
+    saver sub-graph its saver_def names, and the variables / trainable_variables collections of VariableDef protos."""
+    from tensorboard.compat.proto import meta_graph_pb2
+    from distributed_tensorflow_b200.checkpoint.saver import Saver
+    from distributed_tensorflow_b200.models.linear import LinearModel
+    from distributed_tensorflow_b200.optim import get_optimizer
+    from distributed_tensorflow_b200.session import LocalSession
+    sess = LocalSession(LinearModel(), get_optimizer("adam", 0.01))
+    sess.run_init()
+    sess.train_step(np.array([[1.0]]), np.array([[12.0]]))
+    prefix = Saver().save(sess, str(tmp_path / "model.ckpt"), global_step=1)
+    mg = meta_graph_pb2.MetaGraphDef()
+    mg.ParseFromString(open(prefix + ".meta", "rb").read())
+    nodes = {n.name: n for n in mg.graph_def.node}
+    sd = mg.saver_def
+    assert sd.filename_tensor_name.split(":")[0] in nodes and sd.save_tensor_name.split(":")[0] in nodes and sd.restore_op_name in nodes
+    for n in mg.graph_def.node:
+        for i in n.input:
+            assert i.lstrip("^").split(":")[0] in nodes
+    saved = [s.decode() for s in nodes["save/SaveV2/tensor_names"].attr["value"].tensor.string_val]
+    assert saved == ["beta1_power", "beta2_power", "bias", "bias/Adam", "bias/Adam_1", "global_step", "weight", "weight/Adam", "weight/Adam_1"]
+    vdefs = mg.collection_def["variables"].bytes_list.value
+    assert len(vdefs) == 9
+    w = [v for v in vdefs if v.startswith(b"\n\x08weight:0")][0]
+    assert w == b"\n\x08weight:0\x12\rweight/Assign\x1a\rweight/read:02\x16weight/initial_value:08\x01"
+    tv = mg.collection_def["trainable_variables"].bytes_list.value
+    assert sorted(v[2:2 + v[1]] for v in tv) == [b"bias:0", b"weight:0"]

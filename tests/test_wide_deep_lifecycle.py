@@ -72,6 +72,11 @@ def test_three_processes_from_tf_config_train_checkpoint_export_and_ps_auto_stop
         assert np.array_equal(r.get_tensor("embedding")[:51], e0) and np.array_equal(r.get_tensor("embedding/Adagrad")[51:],
                                                                                      r.get_tensor("embedding/part_1/Adagrad"))
     assert 0 <= step <= 80 and e0.shape == (51, 128) and e1.shape == (50, 128)
+    from tensorboard.compat.proto import meta_graph_pb2
+    mg = meta_graph_pb2.MetaGraphDef()
+    mg.ParseFromString(open(ck + ".meta", "rb").read())                      # Saver's .meta next to the checkpoint
+    vars_ = {n.name: [d.size for d in n.attr["shape"].shape.dim] for n in mg.graph_def.node if n.op == "VariableV2"}
+    assert vars_["embedding"] == [101, 128] and vars_["embedding/part_1"] == [50, 128] and mg.saver_def.restore_op_name == "save/restore_all"
     assert e0[0, 0] >= 1.0 and e1[0, 0] >= 2.0                   # rank-specific init, then +0.5 per step
     first = sorted(f for f in os.listdir(os.path.join(tmp, "ckpt")) if f.endswith(".index"))
     assert any(f == "model.ckpt-0.index" for f in first) or len(first) == 5      # immediate first save (kept unless rotated out)
