@@ -58,6 +58,7 @@ def lib() -> C.CDLL:
          C.POINTER(ll), C.POINTER(i), C.POINTER(ll), C.POINTER(ll), C.POINTER(u32))
     _sig(L, "dtfn_bundle_reader_lookup", i, vp, cp)
     _sig(L, "dtfn_bundle_reader_read", i, vp, ll, vp, sz)
+    _sig(L, "dtfn_bundle_reader_num_slices", i, vp, ll)
     _sig(L, "dtfn_bundle_reader_close", None, vp)
     _sig(L, "dtfn_record_writer_open", vp, cp)
     _sig(L, "dtfn_record_writer_write", i, vp, vp, sz)
