@@ -11,8 +11,9 @@ Semantics kept:
 
 * chief: open a session, **restore the latest checkpoint in logdir if there is one, else run
   init_op**; then start the standard services -- a checkpoint thread that saves immediately and
-  then every ``save_model_secs`` (no forced save at exit) and a step-counter thread that writes a
-  ``global_step/sec`` summary to the logdir event file every ``save_summaries_secs`` (120).
+  then every ``save_model_secs`` (no forced save at exit), a step-counter thread that writes a
+  ``global_step/sec`` summary to the logdir event file every ``save_summaries_secs`` (120) and,
+  when ``summary_op`` is given, a summary thread on the same period.
 * non-chief: poll until the model is ready (all variables initialised), every
   ``recovery_wait_secs`` (30), for at most ``max_wait_secs`` (7200).
 * ``managed_session`` stops the services and closes the session on exit and re-raises anything
@@ -214,6 +215,10 @@ class Supervisor:
             if self.summary_writer is None:
                 self.summary_writer = FileWriter(self.logdir)
             threads.append(_StepCounterThread(self, sess))
+        if self.logdir and self.save_summaries_secs and self._summary_op is not None:
+            if self.summary_writer is None:
+                self.summary_writer = FileWriter(self.logdir)
+            threads.append(_SummaryThread(self, sess))
         if self.saver is not None and self.save_model_secs and self.save_path:
             threads.append(_CheckpointThread(self, sess))
         for t in threads:
@@ -271,6 +276,26 @@ class _CheckpointThread(LooperThread):
     def run_loop(self) -> None:
         step = self._sess.global_step() if self._sv._global_step is not None else None
         self._sv.saver.save(self._sess, self._sv.save_path, global_step=step)
+
+
+class _SummaryThread(LooperThread):
+    """SVSummaryThread: every ``save_summaries_secs`` evaluate ``summary_op`` and write it at the current global
+    step.  ``summary_op`` is a callable ``(sess) -> Summary`` (or an iterable of ``(tag, value)``); the reference's
+    task_supervisor.py passes one (:150), task.py passes None (:219-220), which leaves this thread out."""
+
+    def __init__(self, sv: Supervisor, sess):
+        super().__init__(sv.coord, sv.save_summaries_secs, name="SVSummaryThread")
+        self._sv, self._sess = sv, sess
+
+    def run_loop(self) -> None:
+        value = self._sv._summary_op(self._sess)
+        if value is None or self._sv.summary_writer is None:
+            return
+        if not isinstance(value, Summary):
+            value = Summary(value)
+        step = self._sess.global_step() if self._sv._global_step is not None else 0
+        self._sv.summary_writer.add_summary(value, step)
+        self._sv.summary_writer.flush()
 
 
 class _StepCounterThread(LooperThread):

@@ -177,7 +177,12 @@ def _run_distributed(variant, cfg, model, optimizer, train_x, train_y, t0) -> No
     is_chief = task_type == "master"
     saver = Saver(sharded=True) if variant.legacy else Saver()
     recovery_wait = float(_flag(flags, "recovery_wait_secs", 30))
-    sv = Supervisor(is_chief=is_chief, logdir=variant.checkpoint_dir, summary_op=None, saver=saver,
+    # task.py passes summary_op=None (:219-220); task_supervisor.py hands the Supervisor its summary op (:150), which
+    # in TF cannot be evaluated there (it depends on fed placeholders) -- here it is the loss on the first example
+    summary_op = None
+    if variant.legacy:
+        summary_op = lambda s: [("loss", float(s.evaluate(np.array([[train_x[0]]]), np.array([[train_y[0]]]))[0]))]  # noqa: E731
+    sv = Supervisor(is_chief=is_chief, logdir=variant.checkpoint_dir, summary_op=summary_op, saver=saver,
                     global_step=model.global_step_name, save_model_secs=float(_flag(flags, "save_model_secs", 60)),
                     recovery_wait_secs=recovery_wait,
                     session_factory=lambda target: PSSession(model, optimizer, cluster, timeout_ms=timeout_ms,

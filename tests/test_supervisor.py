@@ -175,3 +175,27 @@ def test_chief_restart_restores_without_resetting_live_ps_state_and_publishes_re
     assert worker.is_ready()
     worker.close(), sess.close(), sess2.close()
     srv.stop()
+
+
+def test_summary_thread_writes_summary_op_at_the_global_step(tmp_path):
+    """SVSummaryThread (reference task_supervisor.py:150 passes summary_op to the Supervisor): the chief evaluates
+    it every save_summaries_secs and writes it to the logdir event file at the current global step."""
+    import glob
+    import time
+    import numpy as np
+    from distributed_tensorflow_b200.models.linear import LinearModel
+    from distributed_tensorflow_b200.optim import get_optimizer
+    from distributed_tensorflow_b200.session import LocalSession
+    from distributed_tensorflow_b200.summary import read_events
+    logdir = str(tmp_path / "log")
+    sess0 = LocalSession(LinearModel(), get_optimizer("sgd", 0.01))
+    sv = Supervisor(is_chief=True, logdir=logdir, save_model_secs=0, save_summaries_secs=0.05,
+                    summary_op=lambda s: [("loss", float(s.evaluate(np.array([[1.0]]), np.array([[12.0]]))[0]))],
+                    global_step="global_step", session_factory=lambda t: sess0)
+    with sv.managed_session("") as sess:
+        for _ in range(5):
+            sess.train_step(np.array([[1.0]]), np.array([[12.0]]))
+        time.sleep(0.3)
+    events = [e for f in glob.glob(logdir + "/events.out.tfevents.*") for e in read_events(f)]
+    losses = [(e["step"], v) for e in events for tag, v in e.get("summary", {}).items() if tag == "loss"]
+    assert losses and losses[-1][0] == 5 and 0 < losses[-1][1] < 144.0
