@@ -94,6 +94,8 @@ class TorchWideDeep:
     def _route(self, flat):
         """ids -> (row index at the owner for every received entry [M], bookkeeping to bring rows back)."""
         R, cap = self.world, self.cap
+        if R == 1:
+            return flat, None                                  # one shard: ids are rows, nothing to route
         owner, local = flat % R, flat // R
         order = torch.argsort(owner, stable=True)
         so = owner[order]
@@ -110,6 +112,8 @@ class TorchWideDeep:
 
     def _bring_back(self, x, route):
         """[M, ...] values computed at the owners -> [N, ...] in the order of this rank's ids."""
+        if route is None:
+            return x
         order, slot = route
         back = self._a2a(x.contiguous())
         back = torch.cat([back, torch.zeros_like(back[:1])], 0)      # index R*cap: entries that overflowed
@@ -119,6 +123,8 @@ class TorchWideDeep:
 
     def _send_to_owners(self, g, route):
         """[N, ...] gradients in id order -> [M, ...] aligned with the entries the owner received."""
+        if route is None:
+            return g
         order, slot = route
         send = torch.zeros((self.M + 1,) + tuple(g.shape[1:]), dtype=g.dtype, device=self.dev)
         send.index_copy_(0, slot, g.index_select(0, order))
@@ -194,9 +200,12 @@ class GraphedStep:
         self.s = tuple(torch.empty_like(t) for t in example)
         self.loss = None
         self.graph = None
+        self.first_loss = None
         for _ in range(warmup):                          # allocator warm-up + NCCL connection set-up, outside capture
             self._copy(example)
             self.loss = model.step(*self.s)
+            if self.first_loss is None:
+                self.first_loss = float(self.loss)
         if use_graph and model.dev.type == "cuda":
             try:
                 torch.cuda.synchronize()
@@ -249,7 +258,7 @@ def time_baseline(args, rank, world, dev, group=None, mode="sync", steps=None, u
     pool_h = synthetic_pool(args, rank, pin=dev.type == "cuda")
     pool_d = [tuple(t.to(dev) for t in b) for b in pool_h]
     step = GraphedStep(model, pool_d[0], warmup=max(3, args.warmup), use_graph=use_graph)
-    first_loss = float(step.loss) / args.batch
+    first_loss = step.first_loss / args.batch
 
     def barrier():
         if world > 1:

@@ -315,6 +315,7 @@ def main() -> int:
     # against the fp32 PyTorch oracle on rank 0 (models/wide_deep_verify.py).  It runs after the numbers are
     # taken, under a watchdog that prints the line anyway, so it can never cost the measurement.
     post = {"verify": None, "vs_torch_baseline": None}
+    saved_stdout_box = []                            # set while stdout is redirected (baseline phase), for the watchdog
 
     def emit():
         if rank == 0:
@@ -324,6 +325,10 @@ def main() -> int:
     limit = int(os.environ.get("DTF_BENCH_POST_TIMEOUT", "240"))
 
     def bail():
+        try:
+            os.dup2(saved_stdout_box[0], 1) if saved_stdout_box else None
+        except OSError:
+            pass
         for k in post:
             if post[k] is None:
                 post[k] = {"ok": None, "error": "did not finish within %d s" % limit}
@@ -354,8 +359,12 @@ def main() -> int:
     if os.environ.get("DTF_BENCH_BASELINE", "1") == "0":
         post["vs_torch_baseline"] = {"skipped": "DTF_BENCH_BASELINE=0"}
     else:
+        saved_stdout = os.dup(1)
+        saved_stdout_box.append(saved_stdout)
         try:
             from baseline.wide_deep_torch import time_baseline
+            sys.stdout.flush()
+            os.dup2(2, 1)                            # NCCL prints its version banner on stdout; keep stdout to the one JSON line
             grp = dist.new_group(backend="nccl") if world > 1 else None
             r = time_baseline(args, rank, world, dev, group=grp, mode=args.mode, steps=min(args.steps, 20))
             base_value = global_batch / (r["ms_per_step"] / 1e3)
@@ -367,7 +376,9 @@ def main() -> int:
                 "cuda_graph": r["cuda_graph"], "why_eager": r["why_eager"], "dropped_ids": r["dropped_ids"],
                 "first_loss": r["first_loss"], "last_loss": r["last_loss"]}
         except Exception as e:  # noqa: BLE001
+            os.dup2(saved_stdout, 1)
             fail_soft("vs_torch_baseline", e)
+        os.dup2(saved_stdout, 1)
     dog.cancel()
     emit()
     verify = post["verify"] or {}

@@ -211,15 +211,15 @@ def test_verify_step_two_real_ranks(tmp_path):
     import socket
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     script = tmp_path / "v.py"
-    script.write_text(
-        "import os, json, torch, torch.distributed as dist\\n"
-        "from distributed_tensorflow_b200.models.wide_deep_verify import verify_multi_rank\\n"
-        "r, w = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])\\n"
-        "torch.cuda.set_device(r)\\n"
-        "dist.init_process_group('gloo', rank=r, world_size=w)\\n"
-        "v = verify_multi_rank(r, w, torch.device('cuda', r), dist)\\n"
-        "print('VERIFY ' + json.dumps(v)) if r == 0 else None\\n"
-        "dist.destroy_process_group()\\n")
+    script.write_text("\n".join([
+        "import os, json, torch, torch.distributed as dist",
+        "from distributed_tensorflow_b200.models.wide_deep_verify import verify_multi_rank",
+        "r, w = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])",
+        "torch.cuda.set_device(r)",
+        "dist.init_process_group('gloo', rank=r, world_size=w)",
+        "v = verify_multi_rank(r, w, torch.device('cuda', r), dist)",
+        "if r == 0: print('VERIFY ' + json.dumps(v))",
+        "dist.destroy_process_group()", ""]))
     env = dict(os.environ)
     env["PYTHONPATH"] = REPO
     env.pop("TF_CONFIG", None)
