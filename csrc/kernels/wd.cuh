@@ -33,8 +33,8 @@ struct SlabLayout {
   size_t small_f32;    // [n_small] f32                biases / last layer in fp32, written by owners
   size_t dense_grad;   // [P_pad] f32                  this rank's dense gradient (read by owners)
   size_t mbx_payload;  // [world, cap, 128] bf16       embedding-gradient rows pushed to this shard
-  size_t mbx_rows;     // [world, cap] i32             local row index of each pushed entry
-  size_t mbx_dl;       // [world, cap] f32             wide gradient (dlogit) of each pushed entry
+  size_t mbx_rows;     // [world, cap] i64             per pushed entry: local row index (low 32 bits) | example index at the source (high 32)
+  size_t mbx_dlvec;    // [world, B] f32               dlogit of every example of each source = wide gradient of its entries
   size_t mbx_count;    // [world] u32                  entries published by each source this step
   size_t signal;       // [world * 16] u32             barrier flags
   size_t total;

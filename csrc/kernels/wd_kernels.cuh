@@ -119,7 +119,7 @@ __global__ void wd_dense_broadcast_kernel(const float* __restrict__ master, long
 __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V, PeerTable pt, SlabLayout sl,
                                 long long cap, unsigned int* __restrict__ cnt,
                                 unsigned long long* __restrict__ row_src, unsigned long long* __restrict__ wide_src,
-                                unsigned long long* __restrict__ row_dst, unsigned long long* __restrict__ dl_dst,
+                                unsigned long long* __restrict__ row_dst,
                                 const float* __restrict__ dense_raw, __nv_bfloat16* __restrict__ dense_out, int B,
                                 int dense_in, int dense_pad) {
   __shared__ unsigned int s_cnt[kMaxWorld];
@@ -155,8 +155,10 @@ __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V,
     row_src[e] = reinterpret_cast<unsigned long long>(oslab + sl.emb_bf16) + static_cast<unsigned long long>(lrow) * (kEmbDim * 2);
     wide_src[e] = reinterpret_cast<unsigned long long>(oslab + sl.wide) + static_cast<unsigned long long>(lrow) * 4;
     row_dst[e] = reinterpret_cast<unsigned long long>(oslab + sl.mbx_payload) + entry * (kEmbDim * 2);
-    dl_dst[e] = reinterpret_cast<unsigned long long>(oslab + sl.mbx_dl) + entry * 4;
-    reinterpret_cast<int*>(oslab + sl.mbx_rows)[entry] = static_cast<int>(lrow);
+    // one 8-byte store per entry: where the gradient row goes at the owner, and which of this rank's examples it
+    // belongs to (the owner looks the example's dlogit -- the wide gradient -- up in the vector the loss kernel sends)
+    const long long example = e / (n / B);
+    reinterpret_cast<long long*>(oslab + sl.mbx_rows)[entry] = lrow | (example << 32);
   }
 }
 
@@ -170,7 +172,7 @@ template <bool TRAIN>
 __global__ void __launch_bounds__(256)
 wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict__ mask3, long long ldmask,
                const float* __restrict__ small, int off_w4, int off_b4, int off_wide_b,
-               const float* __restrict__ wide_vals, const unsigned long long* __restrict__ dl_dst,
+               const float* __restrict__ wide_vals, PeerTable pt, SlabLayout sl,
                const float* __restrict__ labels, int B, int F, int H3, float inv_batch,
                float* __restrict__ dlogit, __nv_bfloat16* __restrict__ dz3, float* __restrict__ g_small,
                float* __restrict__ loss_acc, float* __restrict__ prob_out) {
@@ -225,8 +227,9 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
       loss_sum += fmaxf(logit, 0.f) - logit * y + log1pf(__expf(-fabsf(logit)));
       g_b += dl;
     }
-    for (int f = lane; f < F; f += 32)
-      *reinterpret_cast<float*>(dl_dst[static_cast<long long>(m) * F + f]) = dl;  // wide gradient push
+    // wide gradient push: dlogit of this example goes ONCE to every shard (lane r -> rank r) instead of once per
+    // (example, slot) entry; the owners pick it up by the example index stored with each mailbox entry
+    if (lane < pt.world) reinterpret_cast<float*>(pt.slab[lane] + sl.mbx_dlvec)[static_cast<long long>(pt.rank) * B + m] = dl;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       if (c < chunks) {
@@ -333,8 +336,9 @@ wd_colsum_kernel(ColsumJobs jobs) {
 // Mailbox entries of all sources, flattened: entry g belongs to source s with prefix[s] <= g < prefix[s+1].
 struct MailboxView {
   const __nv_bfloat16* payload;  // [world, cap, 128]
-  const int* rows;               // [world, cap]
-  const float* dl;               // [world, cap]
+  const long long* rows;         // [world, cap]  local row (low 32 bits) | example index at the source (high 32)
+  const float* dlvec;            // [world, B]    dlogit of every example of each source
+  int B;
   const unsigned int* count;     // [world]
   long long cap;
   int world;
@@ -373,7 +377,7 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   // two entries per iteration: both rows' loads are in flight before either is updated
   for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += 2 * nwarps) {
-    long long e[2], row[2] = {0, 0}, o[2] = {0, 0};
+    long long e[2], row[2] = {0, 0}, o[2] = {0, 0}, ex[2] = {0, 0};
     bool ok[2];
     uint2 raw[2];
     float4 w[2], a[2], v[2];
@@ -382,7 +386,11 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
     for (int u = 0; u < 2; ++u) {
       const long long g = gi + u * nwarps;
       ok[u] = g < total && mailbox_locate(mv, s_prefix, g, e[u]);
-      if (ok[u]) row[u] = mv.rows[e[u]];
+      if (ok[u]) {
+        const long long packed = mv.rows[e[u]];
+        row[u] = packed & 0xFFFFFFFFll;
+        ex[u] = (e[u] / mv.cap) * mv.B + (packed >> 32);      // [source, example] in the dlogit vectors
+      }
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -396,7 +404,7 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
       if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
       if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
       if (lane == 0) {
-        dlv[u] = mv.dl[e[u]];
+        dlv[u] = mv.dlvec[ex[u]];
         ww[u] = wide[row[u]];
         if (OPT != WD_SGD) wa[u] = wide_s1[row[u]];
         if (opt_has_slot2(OPT)) wv[u] = wide_s2[row[u]];
@@ -449,7 +457,7 @@ wd_sparse_count_kernel(MailboxView mv, unsigned long long* __restrict__ row_stat
   for (long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; g < total;
        g += static_cast<long long>(gridDim.x) * blockDim.x) {
     long long e;
-    if (mailbox_locate(mv, s_prefix, g, e)) atomicAdd(row_state + mv.rows[e], 1ull);
+    if (mailbox_locate(mv, s_prefix, g, e)) atomicAdd(row_state + (mv.rows[e] & 0xFFFFFFFFll), 1ull);
   }
 }
 
@@ -476,7 +484,7 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
   // two entries per iteration; every load that only depends on the row id (gradient, weights,
   // slots, row_state) is issued for both before anything is consumed
   for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += 2 * nwarps) {
-    long long e[2], row[2] = {0, 0}, o[2] = {0, 0};
+    long long e[2], row[2] = {0, 0}, o[2] = {0, 0}, ex[2] = {0, 0};
     bool ok[2];
     uint2 raw[2];
     float4 w[2], a[2], v[2];
@@ -486,7 +494,11 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
     for (int u = 0; u < 2; ++u) {
       const long long g = gi + u * nwarps;
       ok[u] = g < total && mailbox_locate(mv, s_prefix, g, e[u]);
-      if (ok[u]) row[u] = mv.rows[e[u]];
+      if (ok[u]) {
+        const long long packed = mv.rows[e[u]];
+        row[u] = packed & 0xFFFFFFFFll;
+        ex[u] = (e[u] / mv.cap) * mv.B + (packed >> 32);      // [source, example] in the dlogit vectors
+      }
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -500,7 +512,7 @@ wd_sparse_apply_sync_kernel(MailboxView mv, unsigned long long* __restrict__ row
       if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
       if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
       if (lane == 0) {
-        dlv[u] = mv.dl[e[u]];
+        dlv[u] = mv.dlvec[ex[u]];
         ww[u] = wide[row[u]];
         if (OPT != WD_SGD) wa[u] = wide_s1[row[u]];
         if (opt_has_slot2(OPT)) wv[u] = wide_s2[row[u]];

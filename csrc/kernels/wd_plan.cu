@@ -50,7 +50,7 @@ struct dtf_wd_plan {
   __nv_bfloat16 *dZ1 = nullptr, *dZ2 = nullptr, *dZ3 = nullptr;
   uint32_t *m1 = nullptr, *m2 = nullptr, *m3 = nullptr;
   int ldm1 = 0, ldm2 = 0, ldm3 = 0;
-  unsigned long long *row_src = nullptr, *wide_src = nullptr, *row_dst = nullptr, *dl_dst = nullptr;
+  unsigned long long *row_src = nullptr, *wide_src = nullptr, *row_dst = nullptr;
   float* wide_vals = nullptr;   // [B*F] wide weights of the batch's ids, filled by the fused pull
   float* dlogit = nullptr;
   float* prob = nullptr;
@@ -232,8 +232,8 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   sl.small_f32 = take(static_cast<size_t>(dl.n_small + (p->P_pad - dl.P)) * 4);
   sl.dense_grad = take(static_cast<size_t>(p->P_pad) * 4);
   sl.mbx_payload = take(static_cast<size_t>(cfg->world) * sh.cap * kEmbDim * 2);
-  sl.mbx_rows = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
-  sl.mbx_dl = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
+  sl.mbx_rows = take(static_cast<size_t>(cfg->world) * sh.cap * 8);
+  sl.mbx_dlvec = take(static_cast<size_t>(cfg->world) * sh.B * 4);
   sl.mbx_count = take(kMaxWorld * 4);
   sl.signal = take(kMaxWorld * 64);
   p->sl_par[0] = sl;
@@ -242,8 +242,8 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
     SlabLayout& s1 = p->sl_par[1];
     s1.dense_grad = take(static_cast<size_t>(p->P_pad) * 4);
     s1.mbx_payload = take(static_cast<size_t>(cfg->world) * sh.cap * kEmbDim * 2);
-    s1.mbx_rows = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
-    s1.mbx_dl = take(static_cast<size_t>(cfg->world) * sh.cap * 4);
+    s1.mbx_rows = take(static_cast<size_t>(cfg->world) * sh.cap * 8);
+    s1.mbx_dlvec = take(static_cast<size_t>(cfg->world) * sh.B * 4);
     s1.mbx_count = take(kMaxWorld * 4);
   }
   sl.total = off;
@@ -266,8 +266,8 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   p->in_slab<void>("dense_small_f32", sl.small_f32, static_cast<size_t>(dl.n_small) * 4);
   p->in_slab<void>("dense_grad", sl.dense_grad, static_cast<size_t>(p->P_pad) * 4);
   p->in_slab<void>("mbx_payload", sl.mbx_payload, static_cast<size_t>(cfg->world) * sh.cap * kEmbDim * 2);
-  p->in_slab<void>("mbx_rows", sl.mbx_rows, static_cast<size_t>(cfg->world) * sh.cap * 4);
-  p->in_slab<void>("mbx_dl", sl.mbx_dl, static_cast<size_t>(cfg->world) * sh.cap * 4);
+  p->in_slab<void>("mbx_rows", sl.mbx_rows, static_cast<size_t>(cfg->world) * sh.cap * 8);
+  p->in_slab<void>("mbx_dlvec", sl.mbx_dlvec, static_cast<size_t>(cfg->world) * sh.B * 4);
   p->in_slab<void>("mbx_count", sl.mbx_count, kMaxWorld * 4);
   p->in_slab<void>("signal", sl.signal, kMaxWorld * 64);   // barrier pads (diagnostics: bench/stress_overlap.py)
 
@@ -304,7 +304,6 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   ok &= (p->wide_src = p->alloc<unsigned long long>("wide_src", sh.cap)) != nullptr;
   ok &= (p->wide_vals = p->alloc<float>("wide_vals", sh.cap)) != nullptr;
   ok &= (p->row_dst = p->alloc<unsigned long long>("row_dst", sh.cap)) != nullptr;
-  ok &= (p->dl_dst = p->alloc<unsigned long long>("dl_dst", sh.cap)) != nullptr;
   ok &= (p->dlogit = p->alloc<float>("dlogit", B)) != nullptr;
   ok &= (p->prob = p->alloc<float>("prob", B)) != nullptr;
   const int m_tiles = (sh.B + BM - 1) / BM;
@@ -510,7 +509,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   mark(p, st, "begin");
   if (!scratch_zeroed && zero_fill(p->zero_region, p->zero_bytes, st) != 0) return -1;
   DTF_CUDA_OK(launch_kernel(true, wd_route_kernel, dim3((n + 255) / 256), dim3(256), 0, st, ids, n, sh.V, p->pt, p->sl,
-                            sh.cap, p->cnt, p->row_src, p->wide_src, p->row_dst, p->dl_dst, dense_raw, p->dense_x, sh.B,
+                            sh.cap, p->cnt, p->row_src, p->wide_src, p->row_dst, dense_raw, p->dense_x, sh.B,
                             sh.dense_in, sh.dense_pad));
   count_launch();
   mark(p, st, "route+pad");
@@ -563,11 +562,11 @@ static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, boo
   if (train) {
     const size_t smem = 8 * (sh.h3 + 2) * sizeof(float);
     DTF_CUDA_OK(launch_kernel(true, wd_loss_kernel<true>, dim3(grid), dim3(256), smem, st, p->H3, p->m3,
-                              static_cast<long long>(p->ldm3), small, off_w4, off_b4, off_wb, p->wide_vals, p->dl_dst, labels,
+                              static_cast<long long>(p->ldm3), small, off_w4, off_b4, off_wb, p->wide_vals, p->pt, p->sl, labels,
                               sh.B, sh.F, sh.h3, inv_batch, p->dlogit, p->dZ3, g_small, p->loss_acc,
                               static_cast<float*>(nullptr)));
   } else {
-    wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_vals, nullptr,
+    wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_vals, p->pt, p->sl,
                                                 nullptr, sh.B, sh.F, sh.h3, 0.f, nullptr, nullptr, nullptr, nullptr,
                                                 p->prob);
   }
@@ -646,8 +645,9 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st, int which = 3) {
   if (which & 1) {
     MailboxView mv{};
     mv.payload = reinterpret_cast<const __nv_bfloat16*>(p->slab + sl.mbx_payload);
-    mv.rows = reinterpret_cast<const int*>(p->slab + sl.mbx_rows);
-    mv.dl = reinterpret_cast<const float*>(p->slab + sl.mbx_dl);
+    mv.rows = reinterpret_cast<const long long*>(p->slab + sl.mbx_rows);
+    mv.dlvec = reinterpret_cast<const float*>(p->slab + sl.mbx_dlvec);
+    mv.B = p->sh.B;
     mv.count = reinterpret_cast<const unsigned int*>(p->slab + sl.mbx_count);
     mv.cap = p->sh.cap;
     mv.world = p->cfg.world;

@@ -113,7 +113,9 @@ def test_single_rank_step_matches_torch(opt):
     n = cfg.batch * cfg.slots
     cnt = t.buffer("step_scratch", torch.int32)[:1]
     assert int(cnt[0]) == n
-    rows = t.buffer("mbx_rows", torch.int32)[:n].long()
+    packed = t.buffer("mbx_rows", torch.int64)[:n]                 # local row | example index << 32
+    rows = packed & 0xFFFFFFFF
+    assert torch.equal(torch.sort(packed >> 32).values, torch.arange(cfg.batch, device=t.device).repeat_interleave(cfg.slots))
     pay = t.buffer("mbx_payload", torch.bfloat16)[: n * cfg.emb_dim].view(n, cfg.emb_dim).float()
     got = torch.zeros(cfg.emb_rows, cfg.emb_dim, device=t.device).index_add_(0, rows, pay)
     want = torch.zeros(cfg.emb_rows, cfg.emb_dim, device=t.device).index_add_(0, b[0].long().reshape(-1), da.reshape(n, -1))
