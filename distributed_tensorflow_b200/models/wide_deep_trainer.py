@@ -493,7 +493,9 @@ def run_wide_deep(flags, auto_stop: bool = False, trainer_factory=None) -> None:
                     global_step="global_step", save_model_secs=float(getattr(flags, "save_model_secs", 60)),
                     recovery_wait_secs=min(1.0, float(getattr(flags, "recovery_wait_secs", 30))),
                     session_factory=lambda target: session)
-    saver.abort = sv.should_stop
+    # a checkpoint in flight when training ends normally is completed (the other ranks' services stay up until the
+    # chief has stopped); it is only given up when the job is stopping because of an error
+    saver.abort = sv.coord.has_exception
     failed = None
     try:
         ckpt.start_service()               # non-chief ranks answer the chief's checkpoint requests from now on

@@ -55,6 +55,11 @@ class Coordinator:
     def should_stop(self) -> bool:
         return self._stop.is_set()
 
+    def has_exception(self) -> bool:
+        """True when a stop was requested because of an error (not a normal end of training)."""
+        with self._lock:
+            return self._exc is not None
+
     def wait_for_stop(self, timeout: float = None) -> bool:
         return self._stop.wait(timeout)
 
