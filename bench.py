@@ -130,16 +130,36 @@ def main() -> int:
 
     verbose = bool(os.environ.get("DTF_BENCH_VERBOSE"))
 
+    progress = [time.time()]
+
     def say(msg):
+        progress[0] = time.time()
         if verbose:
             print("[rank %d] %s" % (rank, msg), file=sys.stderr, flush=True)
 
+    tr_box = []
     if verbose:
         import faulthandler
-        faulthandler.dump_traceback_later(int(os.environ.get("DTF_BENCH_WATCHDOG", "45")), exit=True)
+        import threading
+        limit = int(os.environ.get("DTF_BENCH_WATCHDOG", "45"))
+
+        def watchdog():
+            # no progress message for `limit` seconds: say where the host is and, with DTF_STAMPS=1, the last
+            # phase marks the device reached
+            while time.time() - progress[0] < limit:
+                time.sleep(1.0)
+            faulthandler.dump_traceback(file=sys.stderr)
+            if tr_box and tr_box[0].stamps_count() > 0:
+                n = tr_box[0].stamps_count()
+                print("[rank %d] stuck; last phase marks (pending = not reached):\n%s" % (rank, tr_box[0].stamps_read(max(0, n - 90), n)),
+                      file=sys.stderr, flush=True)
+            os._exit(1)
+
+        threading.Thread(target=watchdog, daemon=True).start()
     cfg = WideDeepConfig(emb_rows=args.emb_rows, batch=args.batch, optimizer=args.optimizer, sync=(args.mode == "sync"),
                          lr=0.05)
     tr = WideDeepTrainer(cfg, rank=rank, world=world, device=dev)
+    tr_box.append(tr)
     say("trainer created")
     if world > 1:
         tr.attach_peers(dist)
@@ -185,6 +205,7 @@ def main() -> int:
         host_barrier()
         graph = None
         G = 1                                         # steps per graph replay
+        prefetch = args.mode == "async" and os.environ.get("DTF_PREFETCH", "1") != "0"
         if not args.no_graph:
             if args.mode == "async":
                 # Async mode runs the ps-side applies on a second stream that overlaps the next step's
@@ -198,10 +219,17 @@ def main() -> int:
             stream.synchronize()
             tr.overlap_reset()
             graph = torch.cuda.CUDAGraph()
+            stamp_range = [tr.stamps_count(), 0]
+            _lib.reset_launch_count()
             with torch.cuda.graph(graph, stream=stream):
                 for gi in range(G):
-                    tr.step(*statics[gi])
+                    # async: step gi announces step gi+1's inputs, whose rows are then gathered on a low-priority
+                    # stream during step gi (the last step of a replay announces nothing: replays stay self-contained)
+                    nxt = statics[gi + 1][:2] if (prefetch and gi + 1 < G) else None
+                    tr.step(*statics[gi], next_batch=nxt)
                 tr.join()
+            graph_launches = _lib.launch_count()          # kernels of the G captured steps (prefetch kernels included)
+            stamp_range[1] = tr.stamps_count()
             tr.overlap_reset()
             graph.replay()
             stream.synchronize()
@@ -224,6 +252,7 @@ def main() -> int:
         tr.step(s_ids, s_dense, s_labels)          # count the launches of one step outside the graph
         launches_per_step = _lib.launch_count()
         stream.synchronize()
+        launches_total = (graph_launches * (args.steps // G)) if graph is not None else launches_per_step * args.steps
         # Start the clock sampler BEFORE the barrier (spawning nvidia-smi takes tens of ms; doing it
         # after the barrier on rank 0 only would make every other rank's timed region wait for it),
         # then align the GPUs with one untimed step -- its device-side barriers bring all streams to
@@ -238,6 +267,7 @@ def main() -> int:
             for i in range(0, args.steps, G):
                 load_group(pool_d, i)              # device -> device, keeps every step on fresh ids
                 graph.replay()                     # G steps
+                progress[0] = time.time()
         else:
             for i in range(args.steps):
                 load_static(pool_d[i % args.pool])
@@ -249,6 +279,10 @@ def main() -> int:
         dev_ms = e0.elapsed_time(e1)
         if os.environ.get("DTF_BENCH_VERBOSE"):
             print("[rank %d] device-timed arm done: %.3f ms/step" % (rank, dev_ms / args.steps), file=sys.stderr, flush=True)
+        if tr.stamps_count() > 0 and graph is not None:
+            os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(REPO, "gpurun_out", "stamps_%s_n%d_rank%d.txt" % (args.mode, world, rank)), "w") as f:
+                f.write(tr.stamps_read(stamp_range[0], stamp_range[1]))
         # ---------------- end-to-end region: pinned host -> device every step, loss read back -----
         # Through the public training-loop API (models/wide_deep_loop.py): Ge steps per CUDA-graph
         # replay, the graph holding the pinned-host -> device copies of the Ge input batches (copy kernels
@@ -268,6 +302,7 @@ def main() -> int:
         for i in range(0, args.steps, Ge):
             if os.environ.get("DTF_BENCH_VERBOSE") and i % (100 * Ge) == 0:
                 print("[rank %d] e2e replay %d" % (rank, i // Ge), file=sys.stderr, flush=True)
+            progress[0] = time.time()
             loop.run()                             # Ge steps: H2D of their inputs, compute, apply, D2H of the losses
             last_loss = loop.losses()[-1]          # the caller looks at every step's loss (waits for the replay)
         tr.join()
@@ -277,6 +312,7 @@ def main() -> int:
         e2e_ms = e2.elapsed_time(e3)
         e2e_wall_ms = (time.perf_counter() - t0) * 1e3
         clocks = sampler.stop() if sampler else None
+        progress[0] = float("inf")                 # the stall watchdog (verbose runs) covers the timed regions only
 
     t_dev = torch.tensor([dev_ms, max(e2e_ms, e2e_wall_ms)], dtype=torch.float64)
     if world > 1:
@@ -299,13 +335,14 @@ def main() -> int:
                        "parallelism": "ps%d (row-sharded embedding + range-sharded dense, every rank worker+ps)" % world,
                        "mode": args.mode, "optimizer": args.optimizer, "sparse_ids": cfg.slots, "dense_features": cfg.dense_in,
                        "emb_rows": cfg.emb_rows, "cuda_graph": graph is not None, "steps_per_graph": G,
+                       "param_prefetch": bool(prefetch and graph is not None and G > 1),
                        "l2": "per-step working set (55 MB gathered operand + random rows of a 2.5 GB table + 54 MB "
                              "mailbox) exceeds the 126 MB L2; ids change every step"},
             "e2e": {"value": global_batch * args.steps / (e2e_ms / 1e3), "unit": "examples/s",
                     "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4, "steps_per_graph": Ge,
                     "first_loss": first_loss, "last_loss": last_loss},
-            "gpu_launches": int(launches_per_step) * args.steps,
-            "gpu_launches_per_step": int(launches_per_step),
+            "gpu_launches": int(launches_total),
+            "gpu_launches_per_step": round(launches_total / args.steps, 2),
             "clocks": clocks,
         }
     tr.close()

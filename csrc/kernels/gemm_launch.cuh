@@ -24,6 +24,8 @@ struct GemmArgs {
   unsigned long long* tile_flags;
   unsigned int* chunk_counter;
   unsigned long long* trace = nullptr;
+  unsigned long long* dbg = nullptr;   // DTF_GEMM_DBG=1 (see GemmParams::dbg)
+  int dbg_id = 0;
   const unsigned long long* wide_src = nullptr; float* wide_out = nullptr;   // fused pull: side gather of fp32 scalars
   // fused dense pull (B row-sharded over peers)
   const CUtensorMap* b_maps; int b_rows_per_shard;
@@ -87,7 +89,7 @@ int launch_gemm_t(const GemmArgs& a) {
   p.a_buf = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(a.A));
   p.lda_buf = a.lda;
   p.slots = a.slots; p.dense_cols = a.dense_cols;
-  p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter; p.trace = a.trace; p.wide_src = a.wide_src; p.wide_out = a.wide_out;
+  p.tile_flags = a.tile_flags; p.chunk_counter = a.chunk_counter; p.trace = a.trace; p.dbg = a.dbg; p.dbg_id = a.dbg_id; p.wide_src = a.wide_src; p.wide_out = a.wide_out;
   p.row_dst = a.row_dst;
   p.b_maps = a.b_maps; p.b_rows_per_shard = a.b_rows_per_shard;
   const int tiles = ((p.m_tiles + CTAS - 1) / CTAS) * p.n_tiles * p.splits * CTAS;   // in CTAs

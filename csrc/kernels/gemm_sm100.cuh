@@ -65,6 +65,10 @@ struct GemmParams {
   const unsigned long long* wide_src;
   float* wide_out;
   unsigned long long* trace;          // debugging only (bench/pull_trace.py): globaltimer stamps, nullptr = off
+  // debugging only (DTF_GEMM_DBG=1, wd plan): word 0 = number of stall records, words 16 + 4 id + {0,1,2} = CTAs of
+  // launch `dbg_id` that entered / finished set-up / left, from word 128: 4-word records of waits that lasted > 2 s
+  unsigned long long* dbg;
+  int dbg_id;
   // --- fused dense pull (all-gather + GEMM): B is row-sharded over ranks; tile n reads its rows
   //     straight from the owning rank through that rank's tensor map (global memory array) ---
   const CUtensorMap* b_maps;          // [shards] or nullptr
@@ -133,6 +137,31 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // mbarrier wait that, with the debug buffer attached, leaves a record once it has been spinning for 2 s
+  auto wait_bar = [&](uint32_t bar, uint32_t parity, int tag, uint32_t progress) {
+    if (p.dbg == nullptr) {
+      mbar_wait(bar, parity);
+      return;
+    }
+    unsigned long long t0 = 0;
+    bool reported = false;
+    for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin) {
+      if ((spin & 1023u) == 1023u && !reported) {
+        const unsigned long long t = globaltimer_ns();
+        if (t0 == 0ull) t0 = t;
+        else if (t - t0 > 2000000000ull) {
+          const unsigned long long slot = atomicAdd(p.dbg, 1ull) % 96ull;
+          unsigned long long* d = p.dbg + 128 + slot * 4;
+          d[0] = (static_cast<unsigned long long>(p.dbg_id) << 32) | blockIdx.x;
+          d[1] = (static_cast<unsigned long long>(tag) << 32) | static_cast<unsigned int>(warp);
+          d[2] = (static_cast<unsigned long long>(parity) << 32) | bar;
+          d[3] = progress;
+          reported = true;
+        }
+      }
+    }
+  };
+  if (p.dbg != nullptr && threadIdx.x == 0) atomicAdd(p.dbg + 16 + 4 * p.dbg_id, 1ull);
   // tiles are 128 x BN per CTA, 256 x BN per CTA pair; a pair walks one tile sequence together
   const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
   const int m_units = (p.m_tiles + CTAS - 1) / CTAS;
@@ -162,6 +191,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if constexpr (GATHER) st_shared_u32(ready_addr, 0u);
     fence_barrier_init();
   }
+  // Pair: the cta_group::2 allocation acts on the tensor memory of both SMs, so both CTAs must be running before
+  // either warp issues it (and see the end of the kernel for the matching rule on the way out).
+  if constexpr (kPair) cluster_sync_all();
   if (warp == 1) {
     if constexpr (kPair) {
       tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols);
@@ -176,6 +208,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (p.dbg != nullptr && threadIdx.x == 0) atomicAdd(p.dbg + 16 + 4 * p.dbg_id + 1, 1ull);
   // everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the tail of the
   // previous kernel in the stream; its results are needed only from here on
   pdl_launch_dependents();
@@ -224,7 +257,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
           const int s = kiter % kStages;
           const uint32_t ph = (kiter / kStages) & 1;
-          mbar_wait(empty_bar(s), ph ^ 1);
+          wait_bar(empty_bar(s), ph ^ 1, 1, kiter);
           // pair: both CTAs' loads are counted on the leader's barrier, armed by the leader alone
           const uint32_t fbar = kPair ? mapa_shared(full_bar(s), 0) : full_bar(s);
           if (!kPair || cta_rank == 0) mbar_arrive_expect_tx(full_bar(s), CTAS * S::kStageBytes);
@@ -278,13 +311,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int kb0 = s_t * p.k_blocks_per_split;
         const int kb1 = min(total_kb, kb0 + p.k_blocks_per_split);
         const int buf = it & 1;
-        mbar_wait(tempty_bar(buf), ((it >> 1) & 1) ^ 1);
+        wait_bar(tempty_bar(buf), ((it >> 1) & 1) ^ 1, 2, static_cast<uint32_t>(it));
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
         for (int kb = kb0; kb < kb1; ++kb, ++kiter) {
           const int s = kiter % kStages;
           const uint32_t ph = (kiter / kStages) & 1;
-          mbar_wait(full_bar(s), ph);
+          wait_bar(full_bar(s), ph, 3, kiter);
           tc_fence_after();
           const uint32_t sa = smem_base + s * S::kStageBytes;
           const uint32_t sb = sa + S::kABytes;
@@ -341,7 +374,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           pdst[i] = (row < p.M && f < p.slots) ? __ldg(p.row_dst + static_cast<long long>(row) * p.slots + f) : 0ull;
         }
       }
-      mbar_wait(tfull_bar(buf), (it >> 1) & 1);
+      wait_bar(tfull_bar(buf), (it >> 1) & 1, 4, static_cast<uint32_t>(it));
       tc_fence_after();
       if constexpr (GATHER) {
         if (p.trace && warp == 2 && lane == 0) p.trace[65536 + (blockIdx.x * 8 + it) * 4 + 2] = globaltimer_ns();   // MMAs of the tile done
@@ -627,6 +660,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if constexpr (kPair) tmem_dealloc_pair(tmem_base, kTmemCols);
     else tmem_dealloc(tmem_base, kTmemCols);
   }
+  // Pair: neither CTA may exit before BOTH cta_group::2 deallocations have been issued.  An SM whose CTA has left
+  // is handed to the next kernel's CTA at once (programmatic launch, or a kernel of another stream); when that was
+  // a single-CTA GEMM allocating its own tensor memory while the peer's cta_group::2 deallocation was still to
+  // come, the allocator of that SM ended up with columns nobody would free, and a later allocation on it waited
+  // forever (2 GPUs, about one step in 10^4 outside CUDA graphs; bench/stress_tail.py reproduces it in seconds).
+  if constexpr (kPair) cluster_sync_all();
+  if (p.dbg != nullptr && threadIdx.x == 0) atomicAdd(p.dbg + 16 + 4 * p.dbg_id + 2, 1ull);
 }
 
 }  // namespace dtf

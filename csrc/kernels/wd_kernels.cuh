@@ -162,6 +162,74 @@ __global__ void wd_route_kernel(const int* __restrict__ ids, int n, long long V,
   }
 }
 
+// ------------------------------------------------------------------------------------------ prefetch
+// Async mode may fetch the NEXT step's embedding rows while this step's backward pass keeps the tensor cores
+// busy and NVLink idle (a parameter prefetch: the rows are one more step stale, which Hogwild semantics allow).
+// Two small kernels on a low-priority stream: addresses (no mailbox claims -- those stay with the step itself),
+// then a plain gather into the other parity's operand buffer.  The next step then runs GEMM-1 as a plain GEMM.
+__global__ void wd_prefetch_addr_kernel(const int* __restrict__ ids, int n, long long V, PeerTable pt, SlabLayout sl,
+                                        unsigned long long* __restrict__ row_src, unsigned long long* __restrict__ wide_src,
+                                        const float* __restrict__ dense_raw, __nv_bfloat16* __restrict__ a_buf, long long lda,
+                                        int dense_col0, int B, int dense_in, int dense_pad) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B * dense_pad; i += gridDim.x * blockDim.x) {
+    const int m = i / dense_pad, c = i % dense_pad;
+    a_buf[static_cast<long long>(m) * lda + dense_col0 + c] = __float2bfloat16(c < dense_in ? dense_raw[m * dense_in + c] : 0.f);
+  }
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < n) {
+    long long id = ids[e];
+    id %= V;
+    if (id < 0) id += V;
+    const int owner = static_cast<int>(id % pt.world);
+    const long long lrow = id / pt.world;
+    uint8_t* oslab = pt.slab[owner];
+    row_src[e] = reinterpret_cast<unsigned long long>(oslab + sl.emb_bf16) + static_cast<unsigned long long>(lrow) * (kEmbDim * 2);
+    wide_src[e] = reinterpret_cast<unsigned long long>(oslab + sl.wide) + static_cast<unsigned long long>(lrow) * 4;
+  }
+}
+
+// One warp per slice of 16 rows x one slot (256 B per row): 8 unpredicated 16-byte loads per lane from the owners'
+// HBM (local or a peer's over NVLink), stored row-major into the GEMM-1 operand.  256 threads and few registers so
+// that a block fits next to a persistent GEMM CTA (192 threads, up to 168 registers) on the same SM.
+__global__ void __launch_bounds__(256)
+wd_gather_rows_kernel(const unsigned long long* __restrict__ row_src, const unsigned long long* __restrict__ wide_src,
+                      __nv_bfloat16* __restrict__ a_buf, long long lda, float* __restrict__ wide_out, int M, int F) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const long long total = static_cast<long long>((M + 15) / 16) * F;
+  const unsigned long long fallback = reinterpret_cast<unsigned long long>(row_src);   // harmless local address for rows past M
+  for (long long s = warp; s < total; s += nwarps) {
+    const int f = static_cast<int>(s % F);
+    const int row0 = static_cast<int>(s / F) * 16;
+    unsigned long long my_src = fallback;
+    float wv = 0.f;
+    const bool mine = lane < 16 && row0 + lane < M;
+    if (mine) {
+      const long long e = static_cast<long long>(row0 + lane) * F + f;
+      my_src = __ldg(row_src + e);
+      const unsigned long long wa = __ldg(wide_src + e);
+      asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(wv) : "l"(wa));
+    }
+    uint4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int pc = u * 32 + lane;
+      const unsigned long long src = __shfl_sync(0xffffffffu, my_src, pc >> 4);
+      v[u] = ld_global_nc_v4(reinterpret_cast<const uint8_t*>(src) + (pc & 15) * 16);
+    }
+    if (mine) wide_out[static_cast<long long>(row0 + lane) * F + f] = wv;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int pc = u * 32 + lane;
+      const int r = row0 + (pc >> 4);
+      if (r < M)
+        st_global_v4(reinterpret_cast<uint8_t*>(a_buf + static_cast<long long>(r) * lda + f * 128) + (pc & 15) * 16, v[u].x, v[u].y,
+                     v[u].z, v[u].w);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ loss
 // One warp per example: sum of the wide weights (gathered from the owning shards by the fused pull
 // kernel's gather warps), last layer h3 . w4,

@@ -63,6 +63,11 @@ struct dtf_wd_plan {
   // optional per-kernel tracing: CUDA events recorded between launches
   bool profile = false;
   std::vector<std::pair<std::string, cudaEvent_t>> marks;
+  unsigned long long* gemm_dbg = nullptr;    // DTF_GEMM_DBG=1: stall records of the GEMM kernels (GemmParams::dbg)
+  int dbg_id = 0;                            // id the next GEMM launch reports under
+  unsigned long long* stamps = nullptr;      // DTF_STAMPS=1: ring of device-clock stamps, one per mark()
+  std::vector<std::string> stamp_names;
+  long long n_stamp = 0;
   StepState* state = nullptr;  // device: step counter, barrier epoch, optimizer constants
   long long step = 0;          // host mirror of the number of applies issued
   // Async mode double-buffers everything a step hands from its compute phase to its apply phase
@@ -80,6 +85,19 @@ struct dtf_wd_plan {
   bool ev_apply_valid[2] = {false, false};
   int last_compute_parity = 0;
   int apply_blocks_per_sm = 8;   // lowered while the apply shares the SMs with the next step's GEMMs
+  // Async-mode parameter prefetch: the operand buffer and the wide values exist once per step parity; while step t
+  // computes, a low-priority stream gathers step t+1's rows into the other parity's buffers (dtf_wd_set_next_batch).
+  __nv_bfloat16* a_buf_par[2] = {nullptr, nullptr};
+  float* wide_vals_par[2] = {nullptr, nullptr};
+  unsigned long long *row_src_pf = nullptr, *wide_src_pf = nullptr;
+  cudaStream_t pf_stream = nullptr;
+  cudaEvent_t ev_pf[2] = {nullptr, nullptr}, ev_cstart = nullptr;
+  bool pf_valid[2] = {false, false};
+  const int* pf_ids[2] = {nullptr, nullptr};   // the ids pointer a parity's prefetched rows belong to
+  const int* next_ids = nullptr;
+  const float* next_dense = nullptr;
+  int cur_par = 0;
+  long long n_prefetched = 0;                  // steps whose layer 1 ran on prefetched rows
 
   template <typename T>
   T* alloc(const char* name, size_t count) {
@@ -144,8 +162,21 @@ struct NvtxRange {
   }
 };
 
+// DTF_STAMPS=1: every mark also launches a one-thread kernel that writes the device clock into the next slot of
+// a ring, under CUDA-graph capture too (a replay overwrites the slots of its capture), so the timeline of the
+// overlapped streams -- or, read from a second stream while the job is stuck, the last point every stream
+// reached -- can be printed with dtf_wd_stamps_read.  Diagnostics only: the extra kernels cost a few us per step.
+constexpr int kStampCap = 8192;
+__global__ void wd_stamp_kernel(unsigned long long* slot) { *slot = globaltimer_ns(); }
+
 static void mark(dtf_wd_plan* p, cudaStream_t st, const char* name) {
   if (nvtx_on()) nvtxMarkA(name);
+  if (p->stamps != nullptr) {
+    const int idx = static_cast<int>(p->n_stamp % kStampCap);
+    p->stamp_names[idx] = name;
+    p->n_stamp += 1;
+    wd_stamp_kernel<<<1, 1, 0, st>>>(p->stamps + idx);
+  }
   if (!p->profile) return;
   cudaEvent_t e;
   cudaEventCreate(&e);
@@ -160,6 +191,9 @@ static void select_parity(dtf_wd_plan* p, int par) {
   p->chunk_counter = p->zero_region + kMaxWorld;
   p->loss_acc = reinterpret_cast<float*>(p->zero_region + kMaxWorld + 4);
   p->tile_flags = reinterpret_cast<unsigned long long*>(p->zero_region + kMaxWorld + 8);
+  p->a_buf = p->a_buf_par[par];
+  p->wide_vals = p->wide_vals_par[par];
+  p->cur_par = par;
 }
 
 static int mask_ld(int n) {
@@ -288,7 +322,13 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   if (has1) ok &= (p->dense_s1 = p->alloc<float>("dense_slot1", chunk)) != nullptr;
   if (has2) ok &= (p->dense_s2 = p->alloc<float>("dense_slot2", chunk)) != nullptr;
   const size_t B = sh.B;
-  ok &= (p->a_buf = p->alloc<__nv_bfloat16>("a_buf", B * sh.K0)) != nullptr;
+  ok &= (p->a_buf_par[0] = p->alloc<__nv_bfloat16>("a_buf", B * sh.K0)) != nullptr;
+  p->a_buf_par[1] = p->a_buf_par[0];
+  if (!cfg->sync) {
+    ok &= (p->a_buf_par[1] = p->alloc<__nv_bfloat16>("a_buf1", B * sh.K0)) != nullptr;
+    ok &= (p->row_src_pf = p->alloc<unsigned long long>("row_src_pf", sh.cap)) != nullptr;
+    ok &= (p->wide_src_pf = p->alloc<unsigned long long>("wide_src_pf", sh.cap)) != nullptr;
+  }
   ok &= (p->dense_x = p->alloc<__nv_bfloat16>("dense_x", B * sh.dense_pad)) != nullptr;
   ok &= (p->H1 = p->alloc<__nv_bfloat16>("h1", B * sh.h1)) != nullptr;
   ok &= (p->H2 = p->alloc<__nv_bfloat16>("h2", B * sh.h2)) != nullptr;
@@ -302,7 +342,9 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   ok &= (p->m3 = p->alloc<uint32_t>("mask3", B * p->ldm3)) != nullptr;
   ok &= (p->row_src = p->alloc<unsigned long long>("row_src", sh.cap)) != nullptr;
   ok &= (p->wide_src = p->alloc<unsigned long long>("wide_src", sh.cap)) != nullptr;
-  ok &= (p->wide_vals = p->alloc<float>("wide_vals", sh.cap)) != nullptr;
+  ok &= (p->wide_vals_par[0] = p->alloc<float>("wide_vals", sh.cap)) != nullptr;
+  p->wide_vals_par[1] = p->wide_vals_par[0];
+  if (!cfg->sync) ok &= (p->wide_vals_par[1] = p->alloc<float>("wide_vals1", sh.cap)) != nullptr;
   ok &= (p->row_dst = p->alloc<unsigned long long>("row_dst", sh.cap)) != nullptr;
   ok &= (p->dlogit = p->alloc<float>("dlogit", B)) != nullptr;
   ok &= (p->prob = p->alloc<float>("prob", B)) != nullptr;
@@ -312,6 +354,14 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
   if (cfg->sync) p->zero_par[1] = p->zero_par[0];
   else ok &= (p->zero_par[1] = p->alloc<unsigned int>("step_scratch1", kMaxWorld + 8 + m_tiles * kFlagWords * 2 + 8)) != nullptr;
   ok &= (p->state = p->alloc<StepState>("step_state", 1)) != nullptr;
+  if (getenv("DTF_GEMM_DBG") != nullptr && getenv("DTF_GEMM_DBG")[0] == '1') {
+    ok &= (p->gemm_dbg = p->alloc<unsigned long long>("gemm_dbg", 128 + 96 * 4)) != nullptr;
+    if (p->gemm_dbg) cudaMemset(p->gemm_dbg, 0, (128 + 96 * 4) * 8);
+  }
+  if (getenv("DTF_STAMPS") != nullptr && getenv("DTF_STAMPS")[0] == '1') {
+    ok &= (p->stamps = p->alloc<unsigned long long>("stamps", kStampCap)) != nullptr;
+    p->stamp_names.assign(kStampCap, std::string());
+  }
   if (!ok) {
     dtf_wd_destroy(p);
     return nullptr;
@@ -324,6 +374,14 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
       int lo = 0, hi = 0;
       cudaDeviceGetStreamPriorityRange(&lo, &hi);
       cudaStreamCreateWithPriority(&p->side, cudaStreamNonBlocking, hi);
+      // The prefetch stream has the priority of the compute stream: at low priority its blocks were only placed
+      // once the compute stream's chain of back-to-back (programmatic) launches had a gap, ~200 us into the
+      // step, where the gather then shared NVLink with the push (DTF_STAMPS timeline, 2 GPUs).
+      const char* pe = getenv("DTF_PF_PRIO");
+      cudaStreamCreateWithPriority(&p->pf_stream, cudaStreamNonBlocking, (pe != nullptr && pe[0] == '0') ? lo : hi);
+      cudaEventCreateWithFlags(&p->ev_cstart, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&p->ev_pf[0], cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&p->ev_pf[1], cudaEventDisableTiming);
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
       // measured (bench.py, async): 2 GPUs 0.424 -> 0.409 ms with 48 SMs, 8 GPUs 0.473 -> 0.449 ms with 56
@@ -344,6 +402,10 @@ void dtf_wd_destroy(dtf_wd_plan* p) {
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->side) cudaStreamDestroy(p->side);
+  if (p->pf_stream) cudaStreamDestroy(p->pf_stream);
+  if (p->ev_cstart) cudaEventDestroy(p->ev_cstart);
+  for (int i = 0; i < 2; ++i)
+    if (p->ev_pf[i]) cudaEventDestroy(p->ev_pf[i]);
   for (void* m : p->opened) dtf_symm_close_handle(m);
   for (void* q : p->owned) cudaFree(q);
   if (p->slab && p->owns_slab) dtf_symm_free(p->slab);
@@ -501,6 +563,53 @@ static GemmArgs base_args(cudaStream_t st) {
   return a;
 }
 
+// Parameter prefetch of async mode (dtf_wd_set_next_batch): addresses + row gather of the next batch on the
+// low-priority stream, into the operand buffer and wide values of the parity that step will use.  Forked from
+// `st` here (everything the previous user of those buffers launched on `st` is ordered before) and joined by the
+// event the next step's layer 1 waits for.
+static int pf_blocks_per_sm() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DTF_PF_BLOCKS");
+    v = e ? atoi(e) : 2;
+    if (v < 1) v = 1;
+  }
+  return v;
+}
+
+static int launch_prefetch(dtf_wd_plan* p, cudaStream_t st) {
+  const WdShapes& sh = p->sh;
+  const int n = sh.B * sh.F;
+  const int np = p->cur_par ^ 1;
+  DTF_CUDA_OK(cudaEventRecord(p->ev_cstart, st));
+  DTF_CUDA_OK(cudaStreamWaitEvent(p->pf_stream, p->ev_cstart, 0));
+  const int work = n > sh.B * sh.dense_pad ? n : sh.B * sh.dense_pad;
+  mark(p, p->pf_stream, "pf:start");
+  wd_prefetch_addr_kernel<<<(work + 255) / 256, 256, 0, p->pf_stream>>>(
+      p->next_ids, n, sh.V, p->pt, p->sl, p->row_src_pf, p->wide_src_pf, p->next_dense, p->a_buf_par[np],
+      static_cast<long long>(sh.K0), sh.F * kEmbDim, sh.B, sh.dense_in, sh.dense_pad);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  wd_gather_rows_kernel<<<num_sms() * pf_blocks_per_sm(), 256, 0, p->pf_stream>>>(
+      p->row_src_pf, p->wide_src_pf, p->a_buf_par[np], static_cast<long long>(sh.K0), p->wide_vals_par[np], sh.B, sh.F);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  mark(p, p->pf_stream, "pf:gathered");
+  DTF_CUDA_OK(cudaEventRecord(p->ev_pf[np], p->pf_stream));
+  p->pf_valid[np] = true;
+  p->pf_ids[np] = p->next_ids;
+  p->next_ids = nullptr;
+  p->next_dense = nullptr;
+  return 0;
+}
+
+// debug ids of the step's GEMMs: 1 fused pull, 10 layer 1 on prefetched rows, 2-3 layers 2-3, 4 wgrad-3, 5 dgrad-3,
+// 6 wgrad-2, 7 dgrad-2, 8 push, 9 wgrad-1
+static void tag(dtf_wd_plan* p, GemmArgs& a, int id) {
+  a.dbg = p->gemm_dbg;
+  a.dbg_id = id;
+}
+
 static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaStream_t st, bool train,
                    bool scratch_zeroed = false) {
   const WdShapes& sh = p->sh;
@@ -515,19 +624,39 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   mark(p, st, "route+pad");
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
-  // layer 1: embedding pull fused with the GEMM
+  // async mode: start fetching the NEXT step's rows into the other parity's operand buffer
+  if (train && p->next_ids != nullptr && p->pf_stream != nullptr && !p->cfg.sync && launch_prefetch(p, st) != 0) return -1;
+  const int par = p->cur_par;
+  const bool prefetched = train && p->pf_valid[par] && p->pf_ids[par] == ids;
+  if (p->pf_valid[par]) {
+    // whether the rows are used or not (a caller that announced one batch and stepped on another), nothing may
+    // still be writing this parity's buffers when the step touches them
+    DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_pf[par], 0));
+    p->pf_valid[par] = false;
+  }
+  if (p->stamps != nullptr) mark(p, st, prefetched ? "gemm1 may start (prefetched)" : "pull may start");
   GemmArgs a = base_args(st);
   a.A = p->a_buf; a.lda = sh.K0; a.B = W + dl.w1; a.ldb = sh.K0; a.D = p->H1; a.ldd = sh.h1;
   a.M = sh.B; a.N = sh.h1; a.K = sh.K0; a.epi = EPI_BIAS_RELU_BF16; a.bias = small + (dl.b1 - dl.small_begin);
   a.mask_out = train ? p->m1 : nullptr; a.ldmask = p->ldm1;
-  a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
-  a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
-  // the gather warps also fetch the wide weights of the batch's ids (a separate gather kernel on the side
-  // stream next to layers 2-3 measured the same at 2 GPUs and 6 us slower at 1 GPU: run90)
-  a.wide_src = p->wide_src; a.wide_out = p->wide_vals;
   a.bn = 256;
   set_pair(a, 0);
-  if (launch_gemm_gather(a) != 0) return -1;
+  if (prefetched) {
+    // layer 1 on rows a low-priority stream gathered during the previous step: a plain GEMM
+    a.pdl = false;                    // its operand comes from another stream: no early start past the event wait
+    tag(p, a, 10);
+    if (launch_gemm_kk(a) != 0) return -1;
+    p->n_prefetched += 1;
+  } else {
+    // layer 1: embedding pull fused with the GEMM
+    a.gather = true; a.row_src = p->row_src; a.dense_x = p->dense_x; a.slots = sh.F; a.dense_cols = sh.dense_pad;
+    a.tile_flags = p->tile_flags; a.chunk_counter = p->chunk_counter;
+    // the gather warps also fetch the wide weights of the batch's ids (a separate gather kernel on the side
+    // stream next to layers 2-3 measured the same at 2 GPUs and 6 us slower at 1 GPU: run90)
+    a.wide_src = p->wide_src; a.wide_out = p->wide_vals;
+    tag(p, a, 1);
+    if (launch_gemm_gather(a) != 0) return -1;
+  }
   mark(p, st, "pull+gemm1");
   // layers 2, 3
   a = base_args(st);
@@ -536,6 +665,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.mask_out = train ? p->m2 : nullptr; a.ldmask = p->ldm2;
   a.bn = choose_bn(a.M, a.N, 1);
   set_pair(a, 1);
+  tag(p, a, 2);
   if (launch_gemm_kk(a) != 0) return -1;
   a = base_args(st);
   a.A = p->H2; a.lda = sh.h2; a.B = W + dl.w3; a.ldb = sh.h2; a.D = p->H3; a.ldd = sh.h3;
@@ -543,6 +673,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   a.mask_out = train ? p->m3 : nullptr; a.ldmask = p->ldm3;
   a.bn = choose_bn(a.M, a.N, 1);
   set_pair(a, 1);
+  tag(p, a, 3);
   if (launch_gemm_kk(a) != 0) return -1;
   mark(p, st, "gemm2+gemm3");
   return 0;
@@ -603,6 +734,7 @@ static int wgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n_out, const __nv_
     }
   }
   a.splits = splits;
+  tag(p, a, p->dbg_id);
   return launch_gemm_mnmn(a);
 }
 
@@ -613,6 +745,7 @@ static int dgrad(dtf_wd_plan* p, const __nv_bfloat16* dy, int n, const __nv_bflo
   a.M = p->sh.B; a.N = k; a.K = n; a.epi = EPI_DRELU_BF16; a.mask_in = mask; a.ldmask = ldmask;
   a.bn = choose_bn(a.M, a.N, 1);
   set_pair(a, 3);
+  tag(p, a, p->dbg_id);
   return launch_gemm_kmn(a);
 }
 
@@ -787,15 +920,19 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
   if (!defer_wgrad) {
+    p->dbg_id = 4;
     if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
     mark(p, st, "wgrad3");
   }
+  p->dbg_id = 5;
   if (dgrad(p, p->dZ3, sh.h3, W + dl.w3, sh.h2, p->m2, p->ldm2, p->dZ2, st) != 0) return -1;
   mark(p, st, "dgrad3");
   if (!defer_wgrad) {
+    p->dbg_id = 6;
     if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
     mark(p, st, "wgrad2");
   }
+  p->dbg_id = 7;
   if (dgrad(p, p->dZ2, sh.h2, W + dl.w2, sh.h1, p->m1, p->ldm1, p->dZ1, st) != 0) return -1;
   mark(p, st, "dgrad2");
   // fused push: dA = dZ1 W1[:, :F*128]; every 128-wide row goes to its owner's mailbox
@@ -804,6 +941,7 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   a.M = sh.B; a.N = sh.F * kEmbDim; a.K = sh.h1; a.epi = EPI_PUSH_ROWS; a.row_dst = p->row_dst; a.slots = sh.F;
   a.bn = 256;
   set_pair(a, 4);
+  tag(p, a, 8);
   if (defer_wgrad) {
     if (launch_gemm_kmn(a) != 0) return -1;
     mark(p, st, "dgrad1+push");
@@ -819,6 +957,7 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
     a.max_ctas = p->push_ctas;
     a.pdl = false;
     if (launch_gemm_kmn(a) != 0) return -1;
+    mark(p, p->side, "side:push done");
     DTF_CUDA_OK(cudaEventRecord(p->ev_join, p->side));
   }
   (void)grad;
@@ -836,7 +975,9 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
 static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
+  p->dbg_id = 4;
   if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
+  p->dbg_id = 6;
   if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
   return weight_grads(p, st, 0);
 }
@@ -845,6 +986,7 @@ static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
+  p->dbg_id = 9;
   if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st, wgrad1_ctas) != 0) return -1;
   mark(p, st, "wgrad1");
   if (colsum3(p->dZ1, sh.h1, grad + dl.b1, p->dZ2, sh.h2, grad + dl.b2, p->dZ3, sh.h3, grad + dl.b3, sh.B, st) != 0) return -1;
@@ -1030,10 +1172,63 @@ int dtf_wd_join(dtf_wd_plan* p, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   for (int i = 0; i < 2; ++i)
     if (p->ev_apply_valid[i]) DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_apply[i], 0));
+  for (int i = 0; i < 2; ++i)
+    if (p->pf_valid[i]) DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_pf[i], 0));   // an announced batch nobody stepped on yet
   return 0;
 }
 
 // forget cross-step dependencies (call after a full synchronisation, e.g. before capturing a graph)
-void dtf_wd_overlap_reset(dtf_wd_plan* p) { p->ev_apply_valid[0] = p->ev_apply_valid[1] = false; }
+void dtf_wd_overlap_reset(dtf_wd_plan* p) {
+  p->ev_apply_valid[0] = p->ev_apply_valid[1] = false;
+  p->pf_valid[0] = p->pf_valid[1] = false;
+  p->next_ids = nullptr;
+  p->next_dense = nullptr;
+}
+
+// Async mode: announce the batch of the NEXT training step (device pointers that stay valid and unchanged until
+// that step has run).  The coming step then starts a low-priority gather of those rows that overlaps its own
+// backward pass, and the step after runs layer 1 as a plain GEMM on them instead of the fused pull -- provided it
+// is called with the same `ids` pointer; otherwise the prefetched rows are dropped.  The rows are read up to one
+// step earlier than the fused pull would read them (one more step of staleness, which Hogwild training allows);
+// sync-replica plans ignore the call.  Returns 1 if the announcement was taken, 0 if ignored.
+int dtf_wd_set_next_batch(dtf_wd_plan* p, const int* ids, const float* dense_raw) {
+  static const bool off = getenv("DTF_PREFETCH") != nullptr && getenv("DTF_PREFETCH")[0] == '0';
+  if (p->cfg.sync || p->pf_stream == nullptr || off || p->profile) return 0;
+  p->next_ids = ids;
+  p->next_dense = dense_raw;
+  return 1;
+}
+
+long long dtf_wd_prefetched_steps(dtf_wd_plan* p) { return p->n_prefetched; }
+
+// DTF_STAMPS=1 diagnostics.  Count of marks issued so far, and "index name microseconds" lines for the marks
+// [from, to) -- times relative to the earliest of them, 'pending' for a slot the device has not written since
+// `clear` zeroed it.  Reads on a private stream, so it also works while the training streams are stuck.
+long long dtf_wd_stamps_count(dtf_wd_plan* p) { return p->stamps ? p->n_stamp : -1; }
+int dtf_wd_stamps_read(dtf_wd_plan* p, long long from, long long to, int clear, char* buf, size_t cap) {
+  if (p->stamps == nullptr || cap == 0) return -2;
+  static thread_local cudaStream_t probe = nullptr;
+  if (probe == nullptr) DTF_CUDA_OK(cudaStreamCreateWithFlags(&probe, cudaStreamNonBlocking));
+  std::vector<unsigned long long> h(kStampCap);
+  DTF_CUDA_OK(cudaMemcpyAsync(h.data(), p->stamps, kStampCap * 8, cudaMemcpyDeviceToHost, probe));
+  if (clear) DTF_CUDA_OK(cudaMemsetAsync(p->stamps, 0, kStampCap * 8, probe));
+  DTF_CUDA_OK(cudaStreamSynchronize(probe));
+  if (to > p->n_stamp) to = p->n_stamp;
+  if (from < to - kStampCap) from = to - kStampCap;
+  if (from < 0) from = 0;
+  unsigned long long t0 = ~0ull;
+  for (long long i = from; i < to; ++i)
+    if (h[i % kStampCap] != 0ull && h[i % kStampCap] < t0) t0 = h[i % kStampCap];
+  std::string out;
+  char line[160];
+  for (long long i = from; i < to; ++i) {
+    const unsigned long long t = h[i % kStampCap];
+    if (t == 0ull) snprintf(line, sizeof(line), "%lld %s pending\n", i, p->stamp_names[i % kStampCap].c_str());
+    else snprintf(line, sizeof(line), "%lld %s %.1f\n", i, p->stamp_names[i % kStampCap].c_str(), (t - t0) * 1e-3);
+    out += line;
+  }
+  snprintf(buf, cap, "%s", out.c_str());
+  return 0;
+}
 
 }  // extern "C"

@@ -22,7 +22,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 from dataclasses import dataclass, asdict
-from typing import Dict, List, Optional
+from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 import torch
@@ -107,6 +107,9 @@ def _bind(L):
     L.dtf_wd_last_parity.argtypes = [vp]
     L.dtf_wd_step_overlapped.argtypes = [vp, vp, vp, vp, vp, vp]
     L.dtf_wd_join.argtypes = [vp, vp]
+    L.dtf_wd_set_next_batch.argtypes = [vp, vp, vp]
+    L.dtf_wd_prefetched_steps.restype = C.c_longlong
+    L.dtf_wd_prefetched_steps.argtypes = [vp]
     L.dtf_wd_overlap_reset.restype = None
     L.dtf_wd_overlap_reset.argtypes = [vp]
     L.dtf_symm_handle_size.restype = i
@@ -324,14 +327,24 @@ class WideDeepTrainer:
             assert labels.dtype == torch.float32 and labels.numel() == self.cfg.batch
         return C.c_void_p(ids.data_ptr()), C.c_void_p(dense.data_ptr()), C.c_void_p(labels.data_ptr() if labels is not None else 0)
 
-    def step(self, ids: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor, overlap: Optional[bool] = None) -> None:
+    def step(self, ids: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor, overlap: Optional[bool] = None,
+             next_batch: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> None:
         """One full training step on device-resident inputs (asynchronous on the current stream).
 
         In async mode (``cfg.sync == False``) the parameter-server side (barrier + applies) runs on an
-        internal second stream and overlaps the next step's compute phase, unless ``overlap=False``."""
+        internal second stream and overlaps the next step's compute phase, unless ``overlap=False``.
+
+        ``next_batch=(ids, dense)`` (async mode) announces the NEXT step's inputs: device tensors that are
+        already filled on the current stream and stay untouched until that step has run.  Their embedding rows
+        are then gathered on a low-priority stream while this step computes, and the next ``step`` -- called
+        with that same ``ids`` tensor -- runs layer 1 as a plain GEMM on them instead of the fused pull (a
+        parameter prefetch: rows one more step stale, as a TF worker that reads its variables early)."""
         a, b, c = self._ptrs(ids, dense, labels)
         if overlap is None:
             overlap = not self.cfg.sync
+        if next_batch is not None and not self.cfg.sync:
+            na, nb, _ = self._ptrs(next_batch[0], next_batch[1])
+            self._L.dtf_wd_set_next_batch(self._h, na, nb)
         if overlap:
             if self._apply_stream is None:
                 self._apply_stream = torch.cuda.Stream(device=self.device)
@@ -339,6 +352,26 @@ class WideDeepTrainer:
                                                       C.c_void_p(self._apply_stream.cuda_stream)), "dtf_wd_step_overlapped")
         else:
             _lib.check(self._L.dtf_wd_step(self._h, a, b, c, self._stream()), "dtf_wd_step")
+
+    def prefetched_steps(self) -> int:
+        """How many steps ran layer 1 on prefetched rows (see ``step(next_batch=...)``)."""
+        return int(self._L.dtf_wd_prefetched_steps(self._h))
+
+    def stamps_count(self) -> int:
+        """Marks issued so far (``DTF_STAMPS=1`` diagnostics; -1 when off)."""
+        self._L.dtf_wd_stamps_count.restype = C.c_longlong
+        self._L.dtf_wd_stamps_count.argtypes = [C.c_void_p]
+        return int(self._L.dtf_wd_stamps_count(self._h))
+
+    def stamps_read(self, start: int = 0, stop: Optional[int] = None, clear: bool = False) -> str:
+        """``index name microseconds`` per phase mark in [start, stop): the device-side timeline of the
+        overlapped streams.  Reads on a private stream, so it answers while the training streams are stuck."""
+        buf = C.create_string_buffer(1 << 20)
+        self._L.dtf_wd_stamps_read.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong, C.c_int, C.c_char_p, C.c_size_t]
+        stop = self.stamps_count() if stop is None else stop
+        if int(self._L.dtf_wd_stamps_read(self._h, start, stop, int(clear), buf, len(buf))) != 0:
+            return ""
+        return buf.value.decode()
 
     def set_barrier_timeout_ms(self, ms: int) -> None:
         """How long a device barrier waits for a peer before it records an error (0 = forever)."""

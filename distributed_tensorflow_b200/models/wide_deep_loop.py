@@ -18,8 +18,9 @@ with the kernels that spin on peer signals stalled about once per thousand repla
 (``bench/stress_overlap.py``); all-kernel graphs do not.
 
 In async mode the ps-side applies of step t overlap the compute of step t+1 inside the graph
-(:meth:`WideDeepTrainer.step` with ``overlap=True``); the graph ends with a join, so replays are
-self-contained.
+(:meth:`WideDeepTrainer.step` with ``overlap=True``), and step t announces step t+1's batch so that its
+embedding rows are gathered while step t computes (``prefetch``, the default in async mode); the graph
+ends with a join, so replays are self-contained.
 """
 from __future__ import annotations
 
@@ -36,7 +37,7 @@ HostBatch = Tuple[torch.Tensor, torch.Tensor, torch.Tensor]
 
 class GraphedTrainLoop:
     def __init__(self, trainer: WideDeepTrainer, host_batches: Sequence[HostBatch],
-                 stream: Optional[torch.cuda.Stream] = None, warmup: int = 3):
+                 stream: Optional[torch.cuda.Stream] = None, warmup: int = 3, prefetch: Optional[bool] = None):
         if not host_batches:
             raise ValueError("GraphedTrainLoop needs at least one host batch")
         cfg = trainer.cfg
@@ -49,6 +50,9 @@ class GraphedTrainLoop:
                 raise ValueError("dense must be float32 [batch, dense_in]")
             if tuple(labels.shape) != (cfg.batch,) or labels.dtype != torch.float32:
                 raise ValueError("labels must be float32 [batch]")
+        if prefetch is None:                    # async mode: gather step g+1's rows during step g (trainer.step docs)
+            prefetch = not cfg.sync
+        self.prefetch = bool(prefetch)
         self.trainer = trainer
         self.host_batches = list(host_batches)
         self.steps_per_run = len(self.host_batches)
@@ -91,7 +95,11 @@ class GraphedTrainLoop:
                         ready.append(ev)
                 for gi in range(self.steps_per_run):
                     self.stream.wait_event(ready[gi])
-                    trainer.step(*self._dev[gi])
+                    nxt = None
+                    if prefetch and gi + 1 < self.steps_per_run:
+                        self.stream.wait_event(ready[gi + 1])       # the prefetch reads the next batch's ids
+                        nxt = self._dev[gi + 1][:2]
+                    trainer.step(*self._dev[gi], next_batch=nxt)
                     kcopy(self._loss_host[gi:gi + 1], trainer.last_loss_sum(), 1, self.stream)   # device -> pinned host
                 trainer.join()
                 self.stream.wait_stream(self._copy_stream)

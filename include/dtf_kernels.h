@@ -214,6 +214,13 @@ int dtf_wd_step_overlapped(dtf_wd_plan*, const int* ids, const float* dense, con
                            void* compute_stream, void* apply_stream);
 int dtf_wd_join(dtf_wd_plan*, void* stream);      /* stream waits for every apply issued so far */
 void dtf_wd_overlap_reset(dtf_wd_plan*);
+/* async mode: announce the next step's batch so that its rows are gathered (low-priority stream) during the coming
+ * step; 1 = taken, 0 = ignored (sync plan, DTF_PREFETCH=0, profiling) */
+int dtf_wd_set_next_batch(dtf_wd_plan*, const int* ids, const float* dense_raw);
+long long dtf_wd_prefetched_steps(dtf_wd_plan*);   /* steps whose layer 1 ran on prefetched rows */
+/* DTF_STAMPS=1 diagnostics: device-clock stamp at every phase mark, readable while the streams are busy or stuck */
+long long dtf_wd_stamps_count(dtf_wd_plan*);       /* marks issued so far; -1 when stamps are off */
+int dtf_wd_stamps_read(dtf_wd_plan*, long long from, long long to, int clear, char* buf, size_t cap);
 /* per-kernel tracing with CUDA events (the reference only prints wall-clock, trainer/task.py:100-102) */
 void dtf_wd_profile_enable(dtf_wd_plan*, int on);
 int dtf_wd_profile_read(dtf_wd_plan*, char* buf, size_t cap);

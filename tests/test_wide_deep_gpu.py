@@ -257,7 +257,48 @@ def test_graphed_train_loop_trains_from_pinned_host_batches(sync):
     assert ls[-1] < 0.7 * first, (first, ls)
     assert t.global_step() == step0 + 12 * G
     assert loop.h2d_bytes_per_step == cfg.batch * (cfg.slots * 4 + cfg.dense_in * 4 + 4)
+    # async: every step of a replay but the first runs layer 1 on rows prefetched during the step before (the
+    # counter is kept by the host, so it sees the capture, not the replays)
+    assert t.prefetched_steps() == (0 if sync else G - 1)
     t.close()
+
+
+def test_async_parameter_prefetch_feeds_layer_1_the_rows_the_fused_pull_would_fetch():
+    """``step(next_batch=...)``: the next step's rows are gathered on a low-priority stream and layer 1 runs as
+    a plain GEMM on them.  With a zero learning rate the shards never change, so the prefetched operand, the
+    wide values and the loss must equal those of the fused pull; a step on a batch other than the announced one
+    drops the prefetched rows."""
+    cfg = _cfg(sync=False, emb_rows=2000, lr=0.0, optimizer="sgd")
+    seen = {}
+    for pf in (False, True):
+        t = _make(cfg, 1)[0]
+        batches = [_batch(cfg, 100 + s, t.device) for s in range(5)]
+        rec = []
+        for s, b in enumerate(batches):
+            nxt = batches[s + 1][:2] if (pf and s + 1 < len(batches)) else None
+            t.step(*b, next_batch=nxt)
+            t.join()
+            torch.cuda.synchronize()
+            par = int(t._L.dtf_wd_last_parity(t._h))
+            a = t.buffer("a_buf1" if par else "a_buf", torch.bfloat16)[: cfg.batch * t.info.K0].view(cfg.batch, t.info.K0).float().clone()
+            w = t.buffer("wide_vals1" if par else "wide_vals", torch.float32)[: cfg.batch * cfg.slots].clone()
+            h1 = t.buffer("h1", torch.bfloat16)[: cfg.batch * cfg.h1].float().clone()
+            rec.append((float(t.last_loss_sum()), a, w, h1))
+        assert t.prefetched_steps() == (4 if pf else 0)
+        seen[pf] = rec
+        if pf:                                   # announce one batch, step on another: falls back to the fused pull
+            t.step(*batches[0], next_batch=batches[1][:2])
+            t.step(*batches[2])
+            t.join()
+            torch.cuda.synchronize()
+            assert t.prefetched_steps() == 4
+            assert abs(float(t.last_loss_sum()) - seen[False][2][0]) <= 1e-4 * abs(seen[False][2][0])
+        t.close()
+    for s, ((l0, a0, w0, h0), (l1, a1, w1, h1)) in enumerate(zip(seen[False], seen[True])):
+        assert torch.equal(a0, a1), "step %d: prefetched operand differs from the fused pull's" % s
+        assert torch.equal(w0, w1), "step %d: wide values differ" % s
+        _close(h1, h0, 1e-3, 1e-3, "layer-1 output, step %d" % s)
+        assert abs(l0 - l1) <= 1e-4 * abs(l0), (s, l0, l1)
 
 
 @pytest.mark.parametrize("opt", ["adadelta", "ftrl", "rmsprop"])
