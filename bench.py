@@ -140,7 +140,6 @@ def main() -> int:
     tr_box = []
     if verbose:
         import faulthandler
-        import threading
         limit = int(os.environ.get("DTF_BENCH_WATCHDOG", "45"))
 
         def watchdog():

@@ -191,8 +191,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if constexpr (GATHER) st_shared_u32(ready_addr, 0u);
     fence_barrier_init();
   }
-  // Pair: the cta_group::2 allocation acts on the tensor memory of both SMs, so both CTAs must be running before
-  // either warp issues it (and see the end of the kernel for the matching rule on the way out).
+  // Pair: both CTAs must be running before either warp issues the cta_group::2 allocation, which acts on the
+  // tensor memory of both SMs.  Without this cluster barrier a pair now and then never came back from the
+  // allocation (2 GPUs, eager launches: bench/stress_tail.py stalled within ~100 trials of 3 steps, DTF_GEMM_DBG
+  // showed two CTAs of one wgrad launch entered and not set up); with it 12 000 trials ran through.
   if constexpr (kPair) cluster_sync_all();
   if (warp == 1) {
     if constexpr (kPair) {
@@ -660,11 +662,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if constexpr (kPair) tmem_dealloc_pair(tmem_base, kTmemCols);
     else tmem_dealloc(tmem_base, kTmemCols);
   }
-  // Pair: neither CTA may exit before BOTH cta_group::2 deallocations have been issued.  An SM whose CTA has left
-  // is handed to the next kernel's CTA at once (programmatic launch, or a kernel of another stream); when that was
-  // a single-CTA GEMM allocating its own tensor memory while the peer's cta_group::2 deallocation was still to
-  // come, the allocator of that SM ended up with columns nobody would free, and a later allocation on it waited
-  // forever (2 GPUs, about one step in 10^4 outside CUDA graphs; bench/stress_tail.py reproduces it in seconds).
+  // Pair: leave together, after both cta_group::2 deallocations have been issued (a precaution that mirrors the
+  // barrier before the allocation; the stall above was cured by that one, this one alone did not cure it).
   if constexpr (kPair) cluster_sync_all();
   if (p.dbg != nullptr && threadIdx.x == 0) atomicAdd(p.dbg + 16 + 4 * p.dbg_id + 2, 1ull);
 }

@@ -571,7 +571,7 @@ static int pf_blocks_per_sm() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("DTF_PF_BLOCKS");
-    v = e ? atoi(e) : 2;
+    v = e ? atoi(e) : 4;   // 2 GPUs: 0.415 ms/step without prefetch, 0.407 with 2 blocks per SM, 0.398 with 4 or 6
     if (v < 1) v = 1;
   }
   return v;
@@ -610,6 +610,21 @@ static void tag(dtf_wd_plan* p, GemmArgs& a, int id) {
   a.dbg_id = id;
 }
 
+// Where in the step the prefetch of the next batch is forked (DTF_PF_POINT): 0 after the route kernel, 1 after
+// layer 1 has been launched, 2 after the loss kernel.
+static int pf_point() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DTF_PF_POINT");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
+static int maybe_prefetch(dtf_wd_plan* p, cudaStream_t st, int point) {
+  if (point != pf_point() || p->next_ids == nullptr || p->pf_stream == nullptr || p->cfg.sync) return 0;
+  return launch_prefetch(p, st);
+}
+
 static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaStream_t st, bool train,
                    bool scratch_zeroed = false) {
   const WdShapes& sh = p->sh;
@@ -625,7 +640,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
   // async mode: start fetching the NEXT step's rows into the other parity's operand buffer
-  if (train && p->next_ids != nullptr && p->pf_stream != nullptr && !p->cfg.sync && launch_prefetch(p, st) != 0) return -1;
+  if (train && maybe_prefetch(p, st, 0) != 0) return -1;
   const int par = p->cur_par;
   const bool prefetched = train && p->pf_valid[par] && p->pf_ids[par] == ids;
   if (p->pf_valid[par]) {
@@ -658,6 +673,7 @@ static int forward(dtf_wd_plan* p, const int* ids, const float* dense_raw, cudaS
     if (launch_gemm_gather(a) != 0) return -1;
   }
   mark(p, st, "pull+gemm1");
+  if (train && maybe_prefetch(p, st, 1) != 0) return -1;
   // layers 2, 3
   a = base_args(st);
   a.A = p->H1; a.lda = sh.h1; a.B = W + dl.w2; a.ldb = sh.h1; a.D = p->H2; a.ldd = sh.h2;
@@ -917,6 +933,7 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   if (forward(p, ids, dense_raw, st, true, true) != 0) return -1;
   if (launch_loss(p, labels, st, true) != 0) return -1;
   mark(p, st, "loss+wide");
+  if (maybe_prefetch(p, st, 2) != 0) return -1;
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
   if (!defer_wgrad) {

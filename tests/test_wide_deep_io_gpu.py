@@ -230,3 +230,21 @@ def test_verify_step_two_real_ranks(tmp_path):
     import json
     v = json.loads([l for l in p.stdout.splitlines() if l.startswith("VERIFY ")][0][7:])
     assert v["ok"] and v["ranks"] == 2, v
+
+
+def test_two_rank_eager_steps_drain_without_stalling(tmp_path):
+    """Regression for a rare permanent stall of the CTA-pair GEMMs (tensor memory allocated for the pair before
+    the peer CTA was running): 500 times {3 eager overlapped steps, drain the streams} on two real ranks.  Before
+    the fix bench/stress_tail.py stalled within about 100 trials; its watchdog exits non-zero after 12 s."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ)
+    env["PYTHONPATH"] = REPO
+    env.pop("TF_CONFIG", None)
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", str(port), os.path.join(REPO, "bench", "stress_tail.py"), "500", "3"],
+                       cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
+    assert p.stdout.count("500 trials of 3 steps ok") == 2, p.stdout[-2000:]
