@@ -914,6 +914,18 @@ int dtf_wd_profile_read_abs(dtf_wd_plan* p, char* buf, size_t cap) {
 // forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
 // [B*dense_in], labels f32 [B]
 static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas);
+static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas = 0);
+
+// dW3 and dW2 are not on the way to the push: by default they run after the push has been forked to the side
+// stream, next to it, instead of between the data-gradient GEMMs (DTF_LATE_WGRAD=0 restores the old order).
+static bool late_wgrad() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DTF_LATE_WGRAD");
+    v = (e == nullptr || e[0] != '0') ? 1 : 0;
+  }
+  return v == 1;
+}
 
 // defer_wgrad: leave out the weight / bias gradient kernels (the caller runs weight_grads() on another
 // stream) and keep only the chain the sparse push depends on
@@ -936,7 +948,9 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   if (maybe_prefetch(p, st, 2) != 0) return -1;
   const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
-  if (!defer_wgrad) {
+  const bool split = p->push_ctas > 0 && p->push_ctas < num_sms() && !p->profile;
+  const bool late = !defer_wgrad && split && late_wgrad();
+  if (!defer_wgrad && !late) {
     p->dbg_id = 4;
     if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
     mark(p, st, "wgrad3");
@@ -944,7 +958,7 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
   p->dbg_id = 5;
   if (dgrad(p, p->dZ3, sh.h3, W + dl.w3, sh.h2, p->m2, p->ldm2, p->dZ2, st) != 0) return -1;
   mark(p, st, "dgrad3");
-  if (!defer_wgrad) {
+  if (!defer_wgrad && !late) {
     p->dbg_id = 6;
     if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
     mark(p, st, "wgrad2");
@@ -964,7 +978,6 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
     mark(p, st, "dgrad1+push");
     return 0;
   }
-  const bool split = p->push_ctas > 0 && p->push_ctas < num_sms() && !p->profile;
   if (split) {
     // wgrad-1 (tensor-bound) and the push (NVLink-bound once the shards are remote) only depend on
     // dZ1: run them side by side, the push on `push_ctas` SMs of a second stream
@@ -978,7 +991,11 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
     DTF_CUDA_OK(cudaEventRecord(p->ev_join, p->side));
   }
   (void)grad;
-  if (weight_grads(p, st, split ? num_sms() - p->push_ctas : 0) != 0) return -1;
+  if (late) {
+    if (weight_grads_deferred(p, st, num_sms() - p->push_ctas) != 0) return -1;
+  } else if (weight_grads(p, st, split ? num_sms() - p->push_ctas : 0) != 0) {
+    return -1;
+  }
   if (split) {
     DTF_CUDA_OK(cudaStreamWaitEvent(st, p->ev_join, 0));
   } else {
@@ -989,14 +1006,15 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
 }
 
 // dW1 and the three bias gradients (plus dW2, dW3 when they were deferred)
-static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st) {
+static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   p->dbg_id = 4;
-  if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st) != 0) return -1;
+  if (wgrad(p, p->dZ3, sh.h3, p->H2, sh.h2, dl.w3, st, wgrad1_ctas) != 0) return -1;
   p->dbg_id = 6;
-  if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st) != 0) return -1;
-  return weight_grads(p, st, 0);
+  if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st, wgrad1_ctas) != 0) return -1;
+  mark(p, st, "wgrad3+wgrad2");
+  return weight_grads(p, st, wgrad1_ctas);
 }
 
 static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
