@@ -384,9 +384,10 @@ dtf_wd_plan* dtf_wd_create(const dtf_wd_config* cfg) {
       cudaEventCreateWithFlags(&p->ev_pf[1], cudaEventDisableTiming);
       cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
       cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
-      // measured (bench.py, async): 2 GPUs 0.424 -> 0.409 ms with 48 SMs, 8 GPUs 0.473 -> 0.449 ms with 56
+      // measured (bench.py, async): 2 GPUs 0.424 -> 0.409 ms with 48 SMs, 8 GPUs 0.473 -> 0.449 ms with 56;
+      // 1 GPU, with dW3 / dW2 moved next to the push: 0.379 -> 0.370 ms with 56, 0.375 with 40
       const char* e = getenv("DTF_SPLIT_PUSH");
-      p->push_ctas = e ? atoi(e) : (cfg->world > 1 ? 56 : 0);
+      p->push_ctas = e ? atoi(e) : 56;
     }
   }
   return p;
@@ -913,8 +914,8 @@ int dtf_wd_profile_read_abs(dtf_wd_plan* p, char* buf, size_t cap) {
 
 // forward + backward + push of one micro-batch; device pointers: ids int32 [B*F], dense f32
 // [B*dense_in], labels f32 [B]
-static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas);
-static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas = 0);
+static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas, bool with_colsum = true);
+static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas = 0, bool with_colsum = true);
 
 // dW3 and dW2 are not on the way to the push: by default they run after the push has been forked to the side
 // stream, next to it, instead of between the data-gradient GEMMs (DTF_LATE_WGRAD=0 restores the old order).
@@ -988,12 +989,16 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
     a.pdl = false;
     if (launch_gemm_kmn(a) != 0) return -1;
     mark(p, p->side, "side:push done");
+    // the three bias gradients (column sums of dZ1..dZ3, 12 us) follow the push here: the other branch, with the
+    // three weight-gradient GEMMs on the remaining SMs, is the longer one
+    if (colsum3(p->dZ1, sh.h1, grad + dl.b1, p->dZ2, sh.h2, grad + dl.b2, p->dZ3, sh.h3, grad + dl.b3, sh.B, p->side) != 0) return -1;
+    mark(p, p->side, "side:colsum x3");
     DTF_CUDA_OK(cudaEventRecord(p->ev_join, p->side));
   }
   (void)grad;
   if (late) {
-    if (weight_grads_deferred(p, st, num_sms() - p->push_ctas) != 0) return -1;
-  } else if (weight_grads(p, st, split ? num_sms() - p->push_ctas : 0) != 0) {
+    if (weight_grads_deferred(p, st, num_sms() - p->push_ctas, !split) != 0) return -1;
+  } else if (weight_grads(p, st, split ? num_sms() - p->push_ctas : 0, !split) != 0) {
     return -1;
   }
   if (split) {
@@ -1006,7 +1011,7 @@ static int compute_impl(dtf_wd_plan* p, const int* ids, const float* dense_raw, 
 }
 
 // dW1 and the three bias gradients (plus dW2, dW3 when they were deferred)
-static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
+static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas, bool with_colsum) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   p->dbg_id = 4;
@@ -1014,16 +1019,17 @@ static int weight_grads_deferred(dtf_wd_plan* p, cudaStream_t st, int wgrad1_cta
   p->dbg_id = 6;
   if (wgrad(p, p->dZ2, sh.h2, p->H1, sh.h1, dl.w2, st, wgrad1_ctas) != 0) return -1;
   mark(p, st, "wgrad3+wgrad2");
-  return weight_grads(p, st, wgrad1_ctas);
+  return weight_grads(p, st, wgrad1_ctas, with_colsum);
 }
 
-static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas) {
+static int weight_grads(dtf_wd_plan* p, cudaStream_t st, int wgrad1_ctas, bool with_colsum) {
   const WdShapes& sh = p->sh;
   const DenseLayout& dl = p->dl;
   float* grad = reinterpret_cast<float*>(p->slab + p->sl.dense_grad);
   p->dbg_id = 9;
   if (wgrad(p, p->dZ1, sh.h1, p->a_buf, sh.K0, dl.w1, st, wgrad1_ctas) != 0) return -1;
   mark(p, st, "wgrad1");
+  if (!with_colsum) return 0;
   if (colsum3(p->dZ1, sh.h1, grad + dl.b1, p->dZ2, sh.h2, grad + dl.b2, p->dZ3, sh.h3, grad + dl.b3, sh.B, st) != 0) return -1;
   mark(p, st, "colsum x3");
   return 0;
