@@ -236,7 +236,8 @@ wd_gather_rows_kernel(const unsigned long long* __restrict__ row_src, const unsi
 // sigmoid cross-entropy, dlogit; then (training) the wide gradient is written straight into the
 // owners' mailboxes, dZ3 = dlogit * w4 masked by ReLU'(h3), and block-reduced gradients of w4 / b4 /
 // wide bias.  SURVEY.md 2E rows K5, K6.
-template <bool TRAIN>
+// MAXC: register arrays are sized for H3 <= 256 * MAXC (1 for the product shape: 126 -> ~70 registers)
+template <bool TRAIN, int MAXC>
 __global__ void __launch_bounds__(256)
 wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict__ mask3, long long ldmask,
                const float* __restrict__ small, int off_w4, int off_b4, int off_wide_b,
@@ -251,9 +252,9 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
   const int warp = threadIdx.x >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
   const int chunks = H3 / 256;  // 8 elements per lane per chunk
-  float gw4[4][8];
+  float gw4[MAXC][8];
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
+  for (int c = 0; c < MAXC; ++c)
 #pragma unroll
     for (int j = 0; j < 8; ++j) gw4[c][j] = 0.f;
   float g_b = 0.f, loss_sum = 0.f;
@@ -263,9 +264,9 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
     // the wide weights of this example's ids were fetched from their owners by the fused pull
     for (int f = lane; f < F; f += 32) wide += wide_vals[static_cast<long long>(m) * F + f];
     float dot = 0.f;
-    float hv[4][8];
+    float hv[MAXC][8];
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < MAXC; ++c) {
       if (c < chunks) {
         const int col = c * 256 + lane * 8;
         const uint4 raw = *reinterpret_cast<const uint4*>(h3 + static_cast<long long>(m) * H3 + col);
@@ -299,7 +300,7 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
     // (example, slot) entry; the owners pick it up by the example index stored with each mailbox entry
     if (lane < pt.world) reinterpret_cast<float*>(pt.slab[lane] + sl.mbx_dlvec)[static_cast<long long>(pt.rank) * B + m] = dl;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < MAXC; ++c) {
       if (c < chunks) {
         const int col = c * 256 + lane * 8;
         const uint32_t mword = mask3[static_cast<long long>(m) * ldmask + (col >> 5)];
@@ -323,7 +324,7 @@ wd_loss_kernel(const __nv_bfloat16* __restrict__ h3, const uint32_t* __restrict_
   // block reduction of the w4 / b4 / loss partials, one atomic per column per block
   float* mine = s_red + warp * (H3 + 2);
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
+  for (int c = 0; c < MAXC; ++c)
     if (c < chunks)
 #pragma unroll
       for (int j = 0; j < 8; ++j) mine[c * 256 + lane * 8 + j] = gw4[c][j];

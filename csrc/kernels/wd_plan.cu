@@ -704,19 +704,27 @@ static int launch_loss(dtf_wd_plan* p, const float* labels, cudaStream_t st, boo
   const int off_w4 = static_cast<int>(dl.w4 - dl.small_begin), off_b4 = static_cast<int>(dl.b4 - dl.small_begin),
             off_wb = static_cast<int>(dl.wide_b - dl.small_begin);
   const float inv_batch = 1.0f / (static_cast<float>(sh.B) * (p->cfg.sync ? p->cfg.world : 1));
-  static const int loss_mult = getenv("DTF_LOSS_GRID") ? atoi(getenv("DTF_LOSS_GRID")) : 2;
+  // 48 registers since the register arrays are sized by H3 (126 before): four blocks per SM (1 GPU: 0.3599 -> 0.3575 ms)
+  static const int loss_mult = getenv("DTF_LOSS_GRID") ? atoi(getenv("DTF_LOSS_GRID")) : 4;
   int grid = num_sms() * loss_mult;
   if (grid > (sh.B + 7) / 8) grid = (sh.B + 7) / 8;
+  const int maxc = sh.h3 <= 256 ? 1 : (sh.h3 <= 512 ? 2 : 4);
   if (train) {
     const size_t smem = 8 * (sh.h3 + 2) * sizeof(float);
-    DTF_CUDA_OK(launch_kernel(true, wd_loss_kernel<true>, dim3(grid), dim3(256), smem, st, p->H3, p->m3,
-                              static_cast<long long>(p->ldm3), small, off_w4, off_b4, off_wb, p->wide_vals, p->pt, p->sl, labels,
-                              sh.B, sh.F, sh.h3, inv_batch, p->dlogit, p->dZ3, g_small, p->loss_acc,
-                              static_cast<float*>(nullptr)));
+    auto go = [&](auto kern) {
+      return launch_kernel(true, kern, dim3(grid), dim3(256), smem, st, p->H3, p->m3, static_cast<long long>(p->ldm3), small,
+                           off_w4, off_b4, off_wb, p->wide_vals, p->pt, p->sl, labels, sh.B, sh.F, sh.h3, inv_batch, p->dlogit,
+                           p->dZ3, g_small, p->loss_acc, static_cast<float*>(nullptr));
+    };
+    DTF_CUDA_OK(maxc == 1 ? go(wd_loss_kernel<true, 1>) : (maxc == 2 ? go(wd_loss_kernel<true, 2>) : go(wd_loss_kernel<true, 4>)));
   } else {
-    wd_loss_kernel<false><<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_vals, p->pt, p->sl,
-                                                nullptr, sh.B, sh.F, sh.h3, 0.f, nullptr, nullptr, nullptr, nullptr,
-                                                p->prob);
+    auto go = [&](auto kern) {
+      kern<<<grid, 256, 0, st>>>(p->H3, nullptr, 0, small, off_w4, off_b4, off_wb, p->wide_vals, p->pt, p->sl, nullptr, sh.B,
+                                 sh.F, sh.h3, 0.f, nullptr, nullptr, nullptr, nullptr, p->prob);
+    };
+    if (maxc == 1) go(wd_loss_kernel<false, 1>);
+    else if (maxc == 2) go(wd_loss_kernel<false, 2>);
+    else go(wd_loss_kernel<false, 4>);
   }
   DTF_CUDA_OK(cudaGetLastError());
   count_launch();

@@ -8,6 +8,7 @@ example, the F sparse ids followed by the dense features.
 """
 from __future__ import annotations
 
+import os
 import threading
 from typing import Dict
 
@@ -81,7 +82,40 @@ class WideDeepPredictor:
         self._h_ids = torch.zeros(self.max_batch, self.slots, dtype=torch.int32).pin_memory()
         self._h_dense = torch.zeros(self.max_batch, self.dense_in, dtype=torch.float32).pin_memory()
         self._h_out = torch.zeros(self.max_batch, dtype=torch.float32).pin_memory()
+        # One CUDA graph per batch bucket: host -> device copies of the bucket's rows, the forward kernel chain and the
+        # device -> host copy of the probabilities replay as ONE launch (a request of n rows runs in the smallest
+        # bucket >= n; the rows past n hold the previous request's values, which are valid inputs, and are ignored).
+        # DTF_SERVE_GRAPHS=0 keeps the eager launches.
+        self._stream = torch.cuda.Stream(device=dev)
+        self._buckets = [b for b in (1, 16, 64, 256, 1024, 4096) if b < self.max_batch] + [self.max_batch]
+        self._graphs = {}
+        self._use_graphs = os.environ.get("DTF_SERVE_GRAPHS", "1") != "0"
         self.backend = "cuda"
+
+    def _enqueue(self, n: int) -> None:
+        self._ids[:n].copy_(self._h_ids[:n], non_blocking=True)
+        self._dense[:n].copy_(self._h_dense[:n], non_blocking=True)
+        p = self._tr.predict(self._ids, self._dense, n=n)
+        self._h_out[:n].copy_(p, non_blocking=True)
+
+    def _graph_for(self, bucket: int):
+        """The bucket's graph, captured on first use (after one eager run, so that nothing loads lazily under
+        capture); None if capture is refused -- the caller then launches eagerly."""
+        if bucket in self._graphs:
+            return self._graphs[bucket]
+        torch = self._torch
+        g = None
+        try:
+            self._enqueue(bucket)
+            self._stream.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=self._stream):
+                self._enqueue(bucket)
+        except Exception:  # noqa: BLE001
+            g = None
+            self._stream.synchronize()
+        self._graphs[bucket] = g
+        return g
 
     def _predict_gpu(self, ids: np.ndarray, dense: np.ndarray) -> np.ndarray:
         torch = self._torch
@@ -95,11 +129,15 @@ class WideDeepPredictor:
             n = min(self.max_batch, ids.shape[0] - lo)
             self._h_ids[:n].copy_(torch.from_numpy(ids[lo:lo + n]))
             self._h_dense[:n].copy_(torch.from_numpy(dense[lo:lo + n]))
-            self._ids[:n].copy_(self._h_ids[:n], non_blocking=True)
-            self._dense[:n].copy_(self._h_dense[:n], non_blocking=True)
-            p = self._tr.predict(self._ids, self._dense, n=n)
-            self._h_out[:n].copy_(p, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            with torch.cuda.stream(self._stream):
+                g = None
+                if self._use_graphs:
+                    g = self._graph_for(next(b for b in self._buckets if b >= n))
+                if g is not None:
+                    g.replay()
+                else:
+                    self._enqueue(n)
+                self._stream.synchronize()
             out[lo:lo + n] = self._h_out[:n].numpy()
 
     # ------------------------------------------------------------------ CPU
