@@ -292,6 +292,37 @@ __device__ __forceinline__ uint4 ld_global_nc_v4(const void* addr) {
                : "l"(addr));
   return r;
 }
+// Streaming accesses: data touched once per step (optimizer state of a random row, a mailbox entry) is marked
+// evict-first so that it does not push the GEMM operands of the concurrently running step out of L2.
+__device__ __forceinline__ unsigned long long evict_first_policy() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ float4 ld_stream_f4(const float* addr, unsigned long long pol) {
+  float4 r;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(addr), "l"(pol)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ uint2 ld_stream_u2(const void* addr, unsigned long long pol) {
+  uint2 r;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v2.b32 {%0, %1}, [%2], %3;"
+               : "=r"(r.x), "=r"(r.y)
+               : "l"(addr), "l"(pol)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_stream_f4(float* addr, const float4& v, unsigned long long pol) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void st_stream_u2(void* addr, const uint2& v, unsigned long long pol) {
+  asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" ::"l"(addr), "r"(v.x), "r"(v.y), "l"(pol) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

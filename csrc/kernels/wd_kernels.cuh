@@ -425,7 +425,7 @@ __device__ __forceinline__ bool mailbox_locate(const MailboxView& mv, const unsi
 // async (Hogwild): every mailbox entry is applied on its own, straight onto the shard, with no
 // duplicate handling and no locks -- concurrent entries for one row race exactly like
 // use_locking=False in the reference's Apply* ops.
-template <int OPT>
+template <int OPT, bool STREAM>
 __global__ void __launch_bounds__(256)
 wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float* __restrict__ s1,
                                float* __restrict__ s2, __nv_bfloat16* __restrict__ work, float* __restrict__ wide,
@@ -444,6 +444,7 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
   const long long total = s_prefix[mv.world];
   const int lane = threadIdx.x & 31;
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const unsigned long long pol = STREAM ? evict_first_policy() : 0ull;
   // two entries per iteration: both rows' loads are in flight before either is updated
   for (long long gi = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; gi < total; gi += 2 * nwarps) {
     long long e[2], row[2] = {0, 0}, o[2] = {0, 0}, ex[2] = {0, 0};
@@ -468,10 +469,17 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
       wa[u] = wv[u] = 0.f;
       if (!ok[u]) continue;
       o[u] = row[u] * kEmbDim + lane * 4;
-      raw[u] = *reinterpret_cast<const uint2*>(mv.payload + e[u] * kEmbDim + lane * 4);
-      w[u] = *reinterpret_cast<float4*>(master + o[u]);
-      if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
-      if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
+      if (STREAM) {
+        raw[u] = ld_stream_u2(mv.payload + e[u] * kEmbDim + lane * 4, pol);
+        w[u] = ld_stream_f4(master + o[u], pol);
+        if (OPT != WD_SGD) a[u] = ld_stream_f4(s1 + o[u], pol);
+        if (opt_has_slot2(OPT)) v[u] = ld_stream_f4(s2 + o[u], pol);
+      } else {
+        raw[u] = *reinterpret_cast<const uint2*>(mv.payload + e[u] * kEmbDim + lane * 4);
+        w[u] = *reinterpret_cast<float4*>(master + o[u]);
+        if (OPT != WD_SGD) a[u] = *reinterpret_cast<float4*>(s1 + o[u]);
+        if (opt_has_slot2(OPT)) v[u] = *reinterpret_cast<float4*>(s2 + o[u]);
+      }
       if (lane == 0) {
         dlv[u] = mv.dlvec[ex[u]];
         ww[u] = wide[row[u]];
@@ -488,13 +496,20 @@ wd_sparse_apply_entries_kernel(MailboxView mv, float* __restrict__ master, float
       opt_update<OPT>(w[u].y, ga.y, a[u].y, v[u].y, oc);
       opt_update<OPT>(w[u].z, gb.x, a[u].z, v[u].z, oc);
       opt_update<OPT>(w[u].w, gb.y, a[u].w, v[u].w, oc);
-      *reinterpret_cast<float4*>(master + o[u]) = w[u];
-      if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o[u]) = a[u];
-      if (opt_has_slot2(OPT)) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
       uint2 pk;
       pk.x = pack_bf16x2(w[u].x, w[u].y);
       pk.y = pack_bf16x2(w[u].z, w[u].w);
-      *reinterpret_cast<uint2*>(work + o[u]) = pk;
+      if (STREAM) {
+        st_stream_f4(master + o[u], w[u], pol);
+        if (OPT != WD_SGD) st_stream_f4(s1 + o[u], a[u], pol);
+        if (opt_has_slot2(OPT)) st_stream_f4(s2 + o[u], v[u], pol);
+        st_stream_u2(work + o[u], pk, pol);
+      } else {
+        *reinterpret_cast<float4*>(master + o[u]) = w[u];
+        if (OPT != WD_SGD) *reinterpret_cast<float4*>(s1 + o[u]) = a[u];
+        if (opt_has_slot2(OPT)) *reinterpret_cast<float4*>(s2 + o[u]) = v[u];
+        *reinterpret_cast<uint2*>(work + o[u]) = pk;
+      }
       if (lane == 0) {
         opt_update<OPT>(ww[u], dlv[u], wa[u], wv[u], oc);
         wide[row[u]] = ww[u];

@@ -829,8 +829,16 @@ static int apply_t(dtf_wd_plan* p, cudaStream_t st, int which = 3) {
       count_launch(2);
       mark(p, st, "sparse apply (sync)");
     } else {
-      wd_sparse_apply_entries_kernel<OPT><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
-                                                                p->wide_s1, p->wide_s2, oc);
+      // DTF_APPLY_STREAM=1: optimizer state and mailbox entries are read / written with evict-first hints.  Tried
+      // against the idea that the overlapped apply pushes the GEMM operands out of L2: 0.3675 -> 0.3657 ms per step
+      // at one GPU, i.e. within noise, so L2 pollution is not what the overlap costs; left off.
+      static const bool stream_hint = getenv("DTF_APPLY_STREAM") != nullptr && getenv("DTF_APPLY_STREAM")[0] == '1';
+      if (stream_hint)
+        wd_sparse_apply_entries_kernel<OPT, true><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
+                                                                        p->wide_s1, p->wide_s2, oc);
+      else
+        wd_sparse_apply_entries_kernel<OPT, false><<<grid, 256, 0, st>>>(mv, p->emb_master, p->emb_s1, p->emb_s2, work, wide,
+                                                                         p->wide_s1, p->wide_s2, oc);
       count_launch();
       mark(p, st, "sparse apply entries");
     }
