@@ -230,6 +230,85 @@ wd_gather_rows_kernel(const unsigned long long* __restrict__ row_src, const unsi
   }
 }
 
+// ------------------------------------------------------------------------------------------ small-batch forward
+// Serving requests of a few examples (M <= 4 in practice): a 128-row tensor-core tile would be 1-3 % full and the layer is bound
+// by reading W once, so the layer runs as a matrix-vector product on the CUDA cores with the roles swapped -- one
+// warp per OUTPUT NEURON streams its row of W (16-byte loads) against the M activation rows held in shared memory,
+// fp32 accumulation, warp reduction, bias / ReLU, bf16 out.  For layer 1 (X == nullptr) the block first gathers its
+// operand itself: the embedding rows of the ids (addresses from wd_prefetch_addr_kernel, local or on a peer) and
+// the padded dense features; block 0 also fetches the wide weights for the logit kernel.  K must be a multiple of 8.
+template <int MAXM>
+__global__ void __launch_bounds__(256)
+wd_small_layer_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, const unsigned long long* __restrict__ row_src,
+                      const unsigned long long* __restrict__ wide_src, int F, const __nv_bfloat16* __restrict__ dense_x,
+                      int dense_cols, float* __restrict__ wide_out, const __nv_bfloat16* __restrict__ W, long long ldw,
+                      const float* __restrict__ bias, __nv_bfloat16* __restrict__ Y, long long ldy, int M, int N, int K,
+                      int relu) {
+  extern __shared__ uint4 s_x[];   // [M][K / 8]
+  const int kc = K >> 3;
+  if (X != nullptr) {
+    for (int i = threadIdx.x; i < M * kc; i += blockDim.x) {
+      const int m = i / kc, c = i - m * kc;
+      s_x[i] = *reinterpret_cast<const uint4*>(X + static_cast<long long>(m) * ldx + c * 8);
+    }
+  } else {
+    for (int i = threadIdx.x; i < M * kc; i += blockDim.x) {
+      const int m = i / kc, c = i - m * kc;
+      if (c < F * 16) {
+        const unsigned long long src = __ldg(row_src + static_cast<long long>(m) * F + (c >> 4));
+        s_x[i] = ld_global_nc_v4(reinterpret_cast<const uint8_t*>(src) + (c & 15) * 16);
+      } else {
+        s_x[i] = *reinterpret_cast<const uint4*>(dense_x + static_cast<long long>(m) * dense_cols + (c - F * 16) * 8);
+      }
+    }
+    if (blockIdx.x == 0 && wide_out != nullptr)
+      for (int i = threadIdx.x; i < M * F; i += blockDim.x) {
+        float v;
+        asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(__ldg(wide_src + i)));
+        wide_out[i] = v;
+      }
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; n < N; n += warps) {
+    float acc[MAXM];
+#pragma unroll
+    for (int m = 0; m < MAXM; ++m) acc[m] = 0.f;
+    const __nv_bfloat16* wrow = W + static_cast<long long>(n) * ldw;
+#pragma unroll 8
+    for (int c = lane; c < kc; c += 32) {
+      const uint4 wq = ld_global_nc_v4(wrow + c * 8);
+      const __nv_bfloat162* wp = reinterpret_cast<const __nv_bfloat162*>(&wq);
+      float2 wf[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) wf[j] = __bfloat1622float2(wp[j]);
+#pragma unroll
+      for (int m = 0; m < MAXM; ++m) {
+        if (m < M) {
+          const uint4 xq = s_x[m * kc + c];
+          const __nv_bfloat162* xp = reinterpret_cast<const __nv_bfloat162*>(&xq);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 xf = __bfloat1622float2(xp[j]);
+            acc[m] = fmaf(wf[j].x, xf.x, acc[m]);
+            acc[m] = fmaf(wf[j].y, xf.y, acc[m]);
+          }
+        }
+      }
+    }
+    const float bn = bias != nullptr ? __ldg(bias + n) : 0.f;
+#pragma unroll
+    for (int m = 0; m < MAXM; ++m) {
+      if (m < M) {
+        float v = warp_sum(acc[m]) + bn;
+        if (relu) v = fmaxf(v, 0.f);
+        if (lane == 0) Y[static_cast<long long>(m) * ldy + n] = __float2bfloat16(v);
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ loss
 // One warp per example: sum of the wide weights (gathered from the owning shards by the fused pull
 // kernel's gather warps), last layer h3 . w4,

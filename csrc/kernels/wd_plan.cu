@@ -10,6 +10,7 @@
 #include <map>
 #include <string>
 #include <utility>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/dtf_kernels.h"
@@ -1163,6 +1164,62 @@ int dtf_wd_step(dtf_wd_plan* p, const int* ids, const float* dense_raw, const fl
   return 0;
 }
 
+}  // extern "C"
+
+// Forward pass for a handful of examples (n <= 4, serving): addresses, then the three layers as swapped-role
+// matrix-vector kernels (wd_small_layer_kernel) -- 5 launches with the logit kernel, no tensor-core tile that would
+// be 1-12 % full, no scratch to clear.
+template <int MAXM>
+static int small_layer(const __nv_bfloat16* X, long long ldx, const unsigned long long* row_src,
+                       const unsigned long long* wide_src, int F, const __nv_bfloat16* dense_x, int dense_cols,
+                       float* wide_out, const __nv_bfloat16* W, long long ldw, const float* bias, __nv_bfloat16* Y,
+                       long long ldy, int M, int N, int K, cudaStream_t st) {
+  const size_t smem = static_cast<size_t>(M) * K * 2;
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    DTF_CUDA_OK(cudaFuncSetAttribute(wd_small_layer_kernel<MAXM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = 200 * 1024;
+  }
+  int grid = (N + 7) / 8;
+  if (grid > num_sms()) grid = num_sms();
+  wd_small_layer_kernel<MAXM><<<grid, 256, smem, st>>>(X, ldx, row_src, wide_src, F, dense_x, dense_cols, wide_out, W, ldw,
+                                                      bias, Y, ldy, M, N, K, 1);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+static int forward_small(dtf_wd_plan* p, const int* ids, const float* dense_raw, int n, cudaStream_t st) {
+  const WdShapes& sh = p->sh;
+  const DenseLayout& dl = p->dl;
+  const int cnt = n * sh.F;
+  const int work = cnt > n * sh.dense_pad ? cnt : n * sh.dense_pad;
+  // pull addresses of the ids' rows / wide weights, dense features as zero-padded bf16 (no mailbox claims)
+  wd_prefetch_addr_kernel<<<(work + 255) / 256, 256, 0, st>>>(ids, cnt, sh.V, p->pt, p->sl, p->row_src, p->wide_src, dense_raw,
+                                                              p->dense_x, static_cast<long long>(sh.dense_pad), 0, n,
+                                                              sh.dense_in, sh.dense_pad);
+  DTF_CUDA_OK(cudaGetLastError());
+  count_launch();
+  const __nv_bfloat16* W = reinterpret_cast<const __nv_bfloat16*>(p->slab + p->sl.wbf16);
+  const float* small = reinterpret_cast<const float*>(p->slab + p->sl.small_f32);
+  const float *b1 = small + (dl.b1 - dl.small_begin), *b2 = small + (dl.b2 - dl.small_begin), *b3 = small + (dl.b3 - dl.small_begin);
+  auto layers = [&](auto tagm) {
+    constexpr int MM = decltype(tagm)::value;
+    if (small_layer<MM>(nullptr, 0, p->row_src, p->wide_src, sh.F, p->dense_x, sh.dense_pad, p->wide_vals, W + dl.w1, sh.K0, b1,
+                        p->H1, sh.h1, n, sh.h1, sh.K0, st) != 0)
+      return -1;
+    if (small_layer<MM>(p->H1, sh.h1, nullptr, nullptr, 0, nullptr, 0, nullptr, W + dl.w2, sh.h1, b2, p->H2, sh.h2, n, sh.h2,
+                        sh.h1, st) != 0)
+      return -1;
+    return small_layer<MM>(p->H2, sh.h2, nullptr, nullptr, 0, nullptr, 0, nullptr, W + dl.w3, sh.h2, b3, p->H3, sh.h3, n, sh.h3,
+                           sh.h2, st);
+  };
+  if (n == 1) return layers(std::integral_constant<int, 1>{});
+  return layers(std::integral_constant<int, 4>{});
+}
+
+extern "C" {
+
 // serving / evaluation forward: probabilities of the first n examples (n <= batch) into the plan's
 // "prob" buffer.  Small n takes the small-M path of the same kernels: one 128-row tile, TMA
 // zero-fill for the missing rows.
@@ -1175,6 +1232,16 @@ int dtf_wd_predict(dtf_wd_plan* p, const int* ids, const float* dense_raw, int n
   const int full = p->sh.B;
   p->sh.B = n;
   select_parity(p, p->cfg.sync ? 0 : static_cast<int>(p->n_compute & 1));
+  static const bool small_off = getenv("DTF_SERVE_SMALL") != nullptr && getenv("DTF_SERVE_SMALL")[0] == '0';
+  // measured kernel chain (eager launches, 1 GPU): batch 1 76 -> 44 us, batch 4 70 -> 42 us, batch 16 70 -> 80 us (the
+  // 16 activation rows are re-read from shared memory for every row of W), so the path is taken up to 4 examples
+  if (n <= 4 && !small_off && p->sh.K0 % 8 == 0 && p->sh.h1 % 8 == 0 && p->sh.h2 % 8 == 0) {
+    const int rc_small = forward_small(p, ids, dense_raw, n, st);
+    int rc2 = rc_small;
+    if (rc2 == 0) rc2 = launch_loss(p, nullptr, st, false);
+    p->sh.B = full;
+    return rc2;
+  }
   int rc = forward(p, ids, dense_raw, st, false);
   if (rc == 0) rc = launch_loss(p, nullptr, st, false);
   p->sh.B = full;

@@ -87,7 +87,7 @@ class WideDeepPredictor:
         # bucket >= n; the rows past n hold the previous request's values, which are valid inputs, and are ignored).
         # DTF_SERVE_GRAPHS=0 keeps the eager launches.
         self._stream = torch.cuda.Stream(device=dev)
-        self._buckets = [b for b in (1, 16, 64, 256, 1024, 4096) if b < self.max_batch] + [self.max_batch]
+        self._buckets = [b for b in (1, 4, 16, 64, 256, 1024, 4096) if b < self.max_batch] + [self.max_batch]
         self._graphs = {}
         self._use_graphs = os.environ.get("DTF_SERVE_GRAPHS", "1") != "0"
         self.backend = "cuda"
