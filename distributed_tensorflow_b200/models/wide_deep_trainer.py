@@ -505,17 +505,33 @@ def run_wide_deep(flags, auto_stop: bool = False, trainer_factory=None) -> None:
             print("Run training with epoch number: {}".format(flags.max_epochs))
             gen = torch.Generator().manual_seed(100 + d.rank + 7919 * sess.steps)
             steps_per_epoch = max(1, flags.train_steps // max(1, flags.max_epochs))
+            sess_local_steps = [0]             # steps taken by this process (sess.steps also counts restored ones)
             if on_gpu:
                 torch.cuda.set_stream(torch.cuda.Stream(device=tr.device, priority=-1))   # compute outranks the ps-side apply
+            # Async mode on the GPU: the input pipeline runs one batch ahead, and every step announces the next
+            # batch so that its embedding rows are gathered while the step computes (WideDeepTrainer.step).
+            prefetch = on_gpu and not cfg.sync and os.environ.get("DTF_PREFETCH", "1") != "0"
+
+            def draw():
+                batch = synthetic_batch(cfg, gen, torch.device("cpu"))
+                if d.world > 1:
+                    # copy-engine transfers are kept away from the device-barrier kernels of the overlapped apply
+                    # (they stalled intermittently when mixed inside CUDA graphs); the host-side
+                    # batch generation above is far longer than the apply, so this wait is normally already over
+                    tr.join()
+                return tuple(t.to(tr.device) for t in batch)
+
+            total = flags.max_epochs * steps_per_epoch
+            cur = draw()
             for epoch in range(flags.max_epochs):
                 for _ in range(steps_per_epoch):
-                    batch = synthetic_batch(cfg, gen, torch.device("cpu"))
-                    if d.world > 1:
-                        # copy-engine transfers are kept away from the device-barrier kernels of the overlapped apply
-                        # (they stalled intermittently when mixed inside CUDA graphs); the host-side
-                        # batch generation above is far longer than the apply, so this wait is normally already over
-                        tr.join()
-                    tr.step(*(t.to(tr.device) for t in batch))
+                    nxt = draw() if (prefetch and sess_local_steps[0] + 1 < total) else None
+                    if nxt is not None:
+                        tr.step(*cur, next_batch=nxt[:2])
+                    else:
+                        tr.step(*cur)
+                    sess_local_steps[0] += 1
+                    cur = nxt if nxt is not None else (draw() if sess_local_steps[0] < total else None)
                     sess.steps += 1
                 tr.check_error()           # a peer that stopped answering the device barriers: ConnectionError
                 if sv.should_stop():
