@@ -1236,6 +1236,16 @@ int dtf_wd_predict(dtf_wd_plan* p, const int* ids, const float* dense_raw, int n
   // measured kernel chain (eager launches, 1 GPU): batch 1 76 -> 44 us, batch 4 70 -> 42 us, batch 16 70 -> 80 us (the
   // 16 activation rows are re-read from shared memory for every row of W), so the path is taken up to 4 examples
   if (n <= 4 && !small_off && p->sh.K0 % 8 == 0 && p->sh.h1 % 8 == 0 && p->sh.h2 % 8 == 0) {
+    // rows prefetched for the next training step live in this parity's buffers, which the forward below writes
+    // (wide values): wait for the gather and drop it, exactly as forward() does -- that step then pulls again
+    if (p->pf_valid[p->cur_par]) {
+      if (cudaStreamWaitEvent(st, p->ev_pf[p->cur_par], 0) != cudaSuccess) {
+        p->sh.B = full;
+        set_error("dtf_wd_predict: %s", cudaGetErrorString(cudaGetLastError()));
+        return -1;
+      }
+      p->pf_valid[p->cur_par] = false;
+    }
     const int rc_small = forward_small(p, ids, dense_raw, n, st);
     int rc2 = rc_small;
     if (rc2 == 0) rc2 = launch_loss(p, nullptr, st, false);

@@ -293,6 +293,15 @@ def test_async_parameter_prefetch_feeds_layer_1_the_rows_the_fused_pull_would_fe
             torch.cuda.synchronize()
             assert t.prefetched_steps() == 4
             assert abs(float(t.last_loss_sum()) - seen[False][2][0]) <= 1e-4 * abs(seen[False][2][0])
+            # a small predict between the announcement and the step writes this parity's wide values: the pending
+            # gather is waited for and dropped, and the step pulls again
+            t.step(*batches[0], next_batch=batches[1][:2])
+            pr = t.predict(batches[3][0], batches[3][1], n=2).clone()
+            t.step(*batches[1])
+            t.join()
+            torch.cuda.synchronize()
+            assert t.prefetched_steps() == 4 and bool(((pr > 0) & (pr < 1)).all())
+            assert abs(float(t.last_loss_sum()) - seen[False][1][0]) <= 1e-4 * abs(seen[False][1][0])
         t.close()
     for s, ((l0, a0, w0, h0), (l1, a1, w1, h1)) in enumerate(zip(seen[False], seen[True])):
         assert torch.equal(a0, a1), "step %d: prefetched operand differs from the fused pull's" % s
